@@ -1,0 +1,150 @@
+/*
+ * pings_b200 C-ABI — the drop-in boundary of the B200-native PINGS hot path.
+ *
+ * Every entry point takes plain device pointers + sizes + a cudaStream_t (as void*),
+ * returns an int status (PG_OK = 0) and never throws.  No torch types cross this line;
+ * the Python host (pings_b200/*.py) allocates every buffer as a torch tensor and passes
+ * data_ptr()s through ctypes.
+ *
+ * Reference interfaces replaced (paths relative to the reference checkout):
+ *   R3 = submodules/diff-gaussian-rasterization-w-pose
+ *   RS = submodules/diff-gaussian-surfel-rasterization-w-pose
+ *   FS = submodules/fused-ssim
+ *   NP = model/neural_gaussians.py, DEC = model/decoder.py
+ */
+#ifndef PINGS_B200_H_
+#define PINGS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PG_OK 0
+#define PG_ERR_ARG 1        /* bad argument (null pointer, negative size, bad combination) */
+#define PG_ERR_CUDA 2       /* a CUDA runtime call failed; see pg_last_error() */
+#define PG_ERR_UNSUPPORTED 3 /* size outside what the kernels support (e.g. > 65535 tiles) */
+#define PG_ERR_WORKSPACE 4  /* caller-provided workspace too small */
+
+#define PG_VARIANT_3DGS 0
+#define PG_VARIANT_SURFEL 1
+
+/* ABI version; bumped when any struct below changes. */
+int pg_abi_version(void);
+/* Last CUDA error string recorded by this library on the calling thread ("" if none). */
+const char* pg_last_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Rasterizer (3DGS: R3/rasterize_points.h:18-39,41-65,67-70; surfel: RS/rasterize_points.cu:36-60,134-162)
+ * ---------------------------------------------------------------------------------------- */
+
+/* Camera + image settings: the fields of GaussianRasterizationSettings
+ * (R3/diff_gaussian_rasterization/__init__.py:173-186, RS/.../__init__.py:180-196).
+ * All pointers are DEVICE pointers to fp32.  The 4x4 matrices are the 16 floats of the
+ * torch tensor as stored (i.e. the transposed matrix in row-major = column-major math
+ * matrix), exactly what the reference kernels index as m[0],m[4],m[8],m[12]. */
+typedef struct PgRasterParams {
+  int32_t variant;          /* PG_VARIANT_* */
+  int32_t P;                /* number of Gaussians */
+  int32_t sh_degree;        /* D */
+  int32_t sh_coeffs;        /* M = sh.size(1), 0 when colours are precomputed */
+  int32_t image_width, image_height;
+  float tanfovx, tanfovy;
+  float scale_modifier;
+  int32_t prefiltered;
+  int32_t debug;            /* 1: synchronise + check after every launch (CHECK_CUDA, R3 auxiliary.h:166-173) */
+  const float* bg;              /* [3] */
+  const float* viewmatrix;      /* [16] */
+  const float* projmatrix;      /* [16] */
+  const float* projmatrix_raw;  /* [16]  (backward only) */
+  const float* campos;          /* [3]   (SH path only) */
+  /* surfel-only (ignored for 3DGS) */
+  const float* patch_bbox;      /* [4] */
+  const float* prcppoint;       /* [2] */
+  const float* config;          /* [5] surface, normalize_depth, perpix_depth, default, front_only */
+} PgRasterParams;
+
+/* Per-Gaussian inputs; a NULL pointer means "absent" exactly like the reference's empty
+ * tensors (R3 forward.cu:207,243). */
+typedef struct PgGaussians {
+  const float* means3D;        /* [P,3] */
+  const float* shs;            /* [P,M,3] or NULL */
+  const float* colors_precomp; /* [P,3] or NULL */
+  const float* opacities;      /* [P,1] */
+  const float* scales;         /* [P,3] or NULL */
+  const float* rotations;      /* [P,4] or NULL */
+  const float* cov3D_precomp;  /* [P,6] or NULL */
+} PgGaussians;
+
+/* Workspace sizes (bytes).  geom: per-Gaussian state kept for backward; image: per-pixel
+ * state kept for backward + tile ranges; binning: sorted instance lists (R = num_rendered).
+ * Replaces the resize callbacks of R3/rasterize_points.cu:27-33 — no callbacks cross the ABI. */
+size_t pg_raster_geom_bytes(int variant, int P);
+size_t pg_raster_image_bytes(int variant, int width, int height);
+size_t pg_raster_binning_bytes(int variant, int width, int height, int64_t num_rendered);
+
+typedef struct PgRasterFwdOut {
+  float* out_color;     /* [3,H,W]  */
+  float* out_depth;     /* [1,H,W]  */
+  float* out_opacity;   /* [1,H,W]  (3DGS: 1-T; surfel: opac) */
+  int32_t* radii;       /* [P]      */
+  int32_t* n_touched;   /* [P] int, zero-initialised by the caller (3DGS) */
+  float* out_normal;    /* [3,H,W]  surfel only */
+  float* contributions; /* [P] f32, zero-initialised by the caller (surfel) */
+} PgRasterFwdOut;
+
+/* Stage 1: preprocess (K1/K2) + depth ordering + offsets.  Enqueues on `stream`, then waits
+ * only for the 8-byte instance count and returns it in *num_rendered (the one host sync of
+ * the forward, cf. R3 rasterizer_impl.cu:283-284). `radii` is written here. */
+int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g,
+                             void* geom_ws, size_t geom_bytes,
+                             int32_t* radii, int64_t* num_rendered, void* stream);
+/* Stage 2: duplicate + tile binning + ranges + alpha-blend (K5-K8). */
+int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g,
+                             void* geom_ws, void* binning_ws, size_t binning_bytes,
+                             void* image_ws, int64_t num_rendered,
+                             const PgRasterFwdOut* out, void* stream);
+
+typedef struct PgRasterBwdIn {
+  const float* dL_dout_color;   /* [3,H,W] */
+  const float* dL_dout_depth;   /* [1,H,W] */
+  const float* dL_dout_normal;  /* [3,H,W] surfel only */
+  const float* dL_dout_opac;    /* [1,H,W] surfel only */
+  const int32_t* radii;         /* [P] from forward */
+} PgRasterBwdIn;
+
+typedef struct PgRasterBwdOut {   /* all caller-allocated, need NOT be zeroed */
+  float* dL_dmeans2D;   /* [P,3] */
+  float* dL_dcolors;    /* [P,3] */
+  float* dL_dopacity;   /* [P,1] */
+  float* dL_dmeans3D;   /* [P,3] */
+  float* dL_dcov3D;     /* [P,6] */
+  float* dL_dsh;        /* [P,M,3] or NULL */
+  float* dL_dscales;    /* [P,3] */
+  float* dL_drotations; /* [P,4] */
+  float* dL_dtau;       /* [6]  = sum over Gaussians of the reference's [P,6] (rho, theta)   */
+  float* dL_dtau_full;  /* optional [P,6] per-Gaussian pose gradient (reference layout) or NULL */
+} PgRasterBwdOut;
+
+/* Backward (K9-K12): R3/rasterize_points.cu:124-211, RS/rasterize_points.cu:133-233. */
+int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g,
+                       void* geom_ws, void* binning_ws, void* image_ws, int64_t num_rendered,
+                       const PgRasterBwdIn* in, const PgRasterBwdOut* out, void* stream);
+
+/* markVisible (R3/rasterize_points.cu:213-232; RS/rasterize_points.cu:235-254). */
+int pg_mark_visible(int variant, int P, const float* means3D, const float* viewmatrix,
+                    const float* projmatrix, uint8_t* present, void* stream);
+
+/* Debug/parity accessors into the opaque workspaces (device pointers, valid after stage 2). */
+int pg_raster_debug_views(int variant, int P, int width, int height, int64_t num_rendered,
+                          void* geom_ws, void* binning_ws, void* image_ws,
+                          const uint32_t** point_list, const uint32_t** ranges /* uint2[T] */,
+                          const float** final_T, const uint32_t** n_contrib,
+                          const float** records /* float4[3P] */, const uint32_t** depth_sorted_idx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PINGS_B200_H_ */

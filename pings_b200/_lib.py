@@ -1,0 +1,118 @@
+"""ctypes binding of the C-ABI shared library (include/pings_b200.h).
+
+There is no CPU fallback: if libpings_b200.so is missing the import of any op fails loudly.
+Build it with `python -c "import __graft_entry__ as g; g.build()"` or `pings_b200/build.py`.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpings_b200.so")
+
+PG_OK = 0
+PG_VARIANT_3DGS = 0
+PG_VARIANT_SURFEL = 1
+_ERR = {1: "bad argument", 2: "CUDA error", 3: "unsupported size", 4: "workspace too small"}
+
+fp = C.c_void_p  # all device pointers travel as void*
+
+
+class PgRasterParams(C.Structure):
+    _fields_ = [
+        ("variant", C.c_int32), ("P", C.c_int32), ("sh_degree", C.c_int32), ("sh_coeffs", C.c_int32),
+        ("image_width", C.c_int32), ("image_height", C.c_int32),
+        ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("scale_modifier", C.c_float),
+        ("prefiltered", C.c_int32), ("debug", C.c_int32),
+        ("bg", fp), ("viewmatrix", fp), ("projmatrix", fp), ("projmatrix_raw", fp), ("campos", fp),
+        ("patch_bbox", fp), ("prcppoint", fp), ("config", fp),
+    ]
+
+
+class PgGaussians(C.Structure):
+    _fields_ = [("means3D", fp), ("shs", fp), ("colors_precomp", fp), ("opacities", fp), ("scales", fp),
+                ("rotations", fp), ("cov3D_precomp", fp)]
+
+
+class PgRasterFwdOut(C.Structure):
+    _fields_ = [("out_color", fp), ("out_depth", fp), ("out_opacity", fp), ("radii", fp), ("n_touched", fp),
+                ("out_normal", fp), ("contributions", fp)]
+
+
+class PgRasterBwdIn(C.Structure):
+    _fields_ = [("dL_dout_color", fp), ("dL_dout_depth", fp), ("dL_dout_normal", fp), ("dL_dout_opac", fp),
+                ("radii", fp)]
+
+
+class PgRasterBwdOut(C.Structure):
+    _fields_ = [("dL_dmeans2D", fp), ("dL_dcolors", fp), ("dL_dopacity", fp), ("dL_dmeans3D", fp),
+                ("dL_dcov3D", fp), ("dL_dsh", fp), ("dL_dscales", fp), ("dL_drotations", fp), ("dL_dtau", fp),
+                ("dL_dtau_full", fp)]
+
+
+class PingsB200LibraryMissing(ImportError):
+    pass
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise PingsB200LibraryMissing(
+            f"{LIB_PATH} not found: the CUDA extension is not built and pings_b200 has no CPU fallback. "
+            "Run `python -c 'import __graft_entry__ as g; g.build()'` at the repo root.")
+    L = C.CDLL(LIB_PATH)
+    L.pg_abi_version.restype = C.c_int
+    L.pg_last_error.restype = C.c_char_p
+    L.pg_raster_geom_bytes.restype = C.c_size_t
+    L.pg_raster_geom_bytes.argtypes = [C.c_int, C.c_int]
+    L.pg_raster_image_bytes.restype = C.c_size_t
+    L.pg_raster_image_bytes.argtypes = [C.c_int, C.c_int, C.c_int]
+    L.pg_raster_binning_bytes.restype = C.c_size_t
+    L.pg_raster_binning_bytes.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int64]
+    L.pg_mark_visible.restype = C.c_int
+    L.pg_mark_visible.argtypes = [C.c_int, C.c_int, fp, fp, fp, fp, fp]
+    L.pg_raster_forward_stage1.restype = C.c_int
+    L.pg_raster_forward_stage1.argtypes = [C.POINTER(PgRasterParams), C.POINTER(PgGaussians), fp, C.c_size_t, fp,
+                                           C.POINTER(C.c_int64), fp]
+    L.pg_raster_forward_stage2.restype = C.c_int
+    L.pg_raster_forward_stage2.argtypes = [C.POINTER(PgRasterParams), C.POINTER(PgGaussians), fp, fp, C.c_size_t,
+                                           fp, C.c_int64, C.POINTER(PgRasterFwdOut), fp]
+    L.pg_raster_backward.restype = C.c_int
+    L.pg_raster_backward.argtypes = [C.POINTER(PgRasterParams), C.POINTER(PgGaussians), fp, fp, fp, C.c_int64,
+                                     C.POINTER(PgRasterBwdIn), C.POINTER(PgRasterBwdOut), fp]
+    L.pg_raster_debug_views.restype = C.c_int
+    L.pg_raster_debug_views.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, fp, fp, fp] + [C.POINTER(fp)] * 6
+    _declare_optional(L)
+    _lib = L
+    return L
+
+
+def _declare_optional(L: C.CDLL) -> None:
+    """Entry points added by later sources (ssim, neural points); declared when present."""
+    for name, (res, args) in OPTIONAL_SIGNATURES.items():
+        if hasattr(L, name):
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+
+
+OPTIONAL_SIGNATURES: dict = {}
+
+
+def check(rc: int, what: str) -> None:
+    if rc != PG_OK:
+        msg = lib().pg_last_error().decode() if rc == 2 else ""
+        raise RuntimeError(f"pings_b200: {what} failed: {_ERR.get(rc, rc)} {msg}")
+
+
+def ptr(t) -> int | None:
+    """data_ptr of a tensor, or NULL for None / empty tensors (the reference's 'absent' inputs)."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()

@@ -1,0 +1,209 @@
+// C-ABI entry points of the rasterizer (see include/pings_b200.h).
+#include "pg_raster3_bwd.cuh"
+
+namespace pg {
+thread_local char g_last_error[256] = {0};
+
+struct HostSlot {
+  unsigned long long* pinned = nullptr;
+  cudaEvent_t ev = nullptr;
+  int device = -1;
+};
+static thread_local HostSlot g_slot;
+
+static int ensure_slot() {
+  int dev = 0;
+  PG_CUDA(cudaGetDevice(&dev));
+  if (g_slot.pinned && g_slot.device == dev) return PG_OK;
+  if (g_slot.pinned) {
+    cudaFreeHost(g_slot.pinned);
+    cudaEventDestroy(g_slot.ev);
+    g_slot.pinned = nullptr;
+  }
+  PG_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&g_slot.pinned), 64, cudaHostAllocDefault));
+  PG_CUDA(cudaEventCreateWithFlags(&g_slot.ev, cudaEventDisableTiming));
+  g_slot.device = dev;
+  return PG_OK;
+}
+
+static bool params_ok(const PgRasterParams* p) {
+  if (!p) return false;
+  if (p->variant != PG_VARIANT_3DGS && p->variant != PG_VARIANT_SURFEL) return false;
+  if (p->P < 0 || p->image_width <= 0 || p->image_height <= 0) return false;
+  if (!p->viewmatrix || !p->projmatrix || !p->bg) return false;
+  return true;
+}
+}  // namespace pg
+
+using namespace pg;
+
+extern "C" {
+
+int pg_abi_version(void) { return 1; }
+const char* pg_last_error(void) { return g_last_error; }
+
+size_t pg_raster_geom_bytes(int variant, int P) { return carve_geom(variant, P, nullptr, nullptr); }
+size_t pg_raster_image_bytes(int variant, int width, int height) {
+  return carve_image(variant, width, height, nullptr, nullptr);
+}
+size_t pg_raster_binning_bytes(int variant, int width, int height, int64_t num_rendered) {
+  (void)variant; (void)width; (void)height;
+  return carve_binning(num_rendered, nullptr, nullptr);
+}
+
+int pg_mark_visible(int variant, int P, const float* means3D, const float* viewmatrix,
+                    const float* projmatrix, uint8_t* present, void* stream) {
+  (void)projmatrix;
+  if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return PG_ERR_ARG;
+  if (variant != PG_VARIANT_3DGS) return PG_ERR_UNSUPPORTED;
+  if (P == 0) return PG_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  r3_mark_visible_kernel<<<div_up(P, 256), 256, 0, st>>>(P, means3D, viewmatrix, present);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, size_t geom_bytes,
+                             int32_t* radii, int64_t* num_rendered, void* stream) {
+  if (!params_ok(prm) || !g || !num_rendered) return PG_ERR_ARG;
+  *num_rendered = 0;
+  const int P = prm->P;
+  if (P == 0) return PG_OK;
+  if (!geom_ws || !radii || !g->means3D || !g->opacities) return PG_ERR_ARG;
+  if (!g->colors_precomp && !g->shs) return PG_ERR_ARG;
+  if (!g->cov3D_precomp && (!g->scales || !g->rotations)) return PG_ERR_ARG;
+  if (!g->colors_precomp && !prm->campos) return PG_ERR_ARG;
+  if (prm->variant != PG_VARIANT_3DGS) return PG_ERR_UNSUPPORTED;
+  const int W = prm->image_width, H = prm->image_height;
+  const int gx = div_up(W, kTile), gy = div_up(H, kTile);
+  if ((int64_t)gx * gy > 65535) return PG_ERR_UNSUPPORTED;
+  if (geom_bytes < carve_geom(prm->variant, P, nullptr, nullptr)) return PG_ERR_WORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = ensure_slot();
+  if (rc != PG_OK) return rc;
+  GeomWs ws;
+  carve_geom(prm->variant, P, geom_ws, &ws);
+  PG_CUDA(cudaMemsetAsync(ws.total, 0, sizeof(unsigned long long), st));
+  R3PreArgs a;
+  a.P = P; a.D = prm->sh_degree; a.M = prm->sh_coeffs; a.W = W; a.H = H; a.gx = gx; a.gy = gy;
+  a.means = g->means3D; a.scales = g->scales; a.rots = g->rotations; a.opac = g->opacities; a.shs = g->shs;
+  a.cov3D_pre = g->cov3D_precomp; a.colors_pre = g->colors_precomp;
+  a.view = prm->viewmatrix; a.proj = prm->projmatrix; a.campos = prm->campos;
+  a.mod = prm->scale_modifier; a.tanx = prm->tanfovx; a.tany = prm->tanfovy;
+  a.fx = W / (2.0f * prm->tanfovx);
+  a.fy = H / (2.0f * prm->tanfovy);
+  a.prefiltered = prm->prefiltered;
+  r3_preprocess_kernel<<<div_up(P, 256), 256, 0, st>>>(a, radii, ws.rec, ws.dkey, ws.tiles, ws.rect, ws.clamped,
+                                                      ws.total);
+  PG_LAUNCH_CHECK(prm->debug, st);
+  PG_CUDA(cudaMemcpyAsync(g_slot.pinned, ws.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  PG_CUDA(cudaEventRecord(g_slot.ev, st));
+  // depth ordering runs while the host waits for the count
+  PG_CUDA(depth_order_and_offsets(ws, P, st));
+  PG_LAUNCH_CHECK(prm->debug, st);
+  PG_CUDA(cudaEventSynchronize(g_slot.ev));
+  const unsigned long long R = *g_slot.pinned;
+  if (R > 0xfffffff0ull) return PG_ERR_UNSUPPORTED;
+  *num_rendered = (int64_t)R;
+  return PG_OK;
+}
+
+int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, void* binning_ws,
+                             size_t binning_bytes, void* image_ws, int64_t num_rendered,
+                             const PgRasterFwdOut* out, void* stream) {
+  if (!params_ok(prm) || !g || !out || num_rendered < 0) return PG_ERR_ARG;
+  if (prm->variant != PG_VARIANT_3DGS) return PG_ERR_UNSUPPORTED;
+  if (!image_ws || !out->out_color || !out->out_depth || !out->out_opacity) return PG_ERR_ARG;
+  const int P = prm->P, W = prm->image_width, H = prm->image_height;
+  const int gx = div_up(W, kTile), gy = div_up(H, kTile);
+  if ((int64_t)gx * gy > 65535) return PG_ERR_UNSUPPORTED;
+  if (P > 0 && (!geom_ws || !out->n_touched)) return PG_ERR_ARG;
+  if (num_rendered > 0 && (!binning_ws || binning_bytes < carve_binning(num_rendered, nullptr, nullptr)))
+    return PG_ERR_WORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  GeomWs gw;
+  BinWs bw;
+  ImageWs iw;
+  carve_geom(prm->variant, P, geom_ws, &gw);
+  carve_binning(num_rendered, binning_ws, &bw);
+  carve_image(prm->variant, W, H, image_ws, &iw);
+  const uint32_t* point_list = nullptr;
+  PG_CUDA(bin_instances(gw, bw, iw, P, W, H, num_rendered, &point_list, st));
+  PG_LAUNCH_CHECK(prm->debug, st);
+  r3_render_fwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
+                                                      out->out_color, out->out_depth, out->out_opacity, iw.final_T,
+                                                      iw.n_contrib, out->n_touched);
+  PG_LAUNCH_CHECK(prm->debug, st);
+  return PG_OK;
+}
+
+int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, void* binning_ws,
+                       void* image_ws, int64_t num_rendered, const PgRasterBwdIn* in, const PgRasterBwdOut* out,
+                       void* stream) {
+  if (!params_ok(prm) || !g || !in || !out || num_rendered < 0) return PG_ERR_ARG;
+  if (prm->variant != PG_VARIANT_3DGS) return PG_ERR_UNSUPPORTED;
+  const int P = prm->P, W = prm->image_width, H = prm->image_height;
+  if (P == 0) {
+    if (out->dL_dtau) PG_CUDA(cudaMemsetAsync(out->dL_dtau, 0, 6 * sizeof(float), (cudaStream_t)stream));
+    return PG_OK;
+  }
+  if (!geom_ws || !image_ws || !in->dL_dout_color || !in->dL_dout_depth || !in->radii || !prm->projmatrix_raw)
+    return PG_ERR_ARG;
+  if (!out->dL_dmeans2D || !out->dL_dcolors || !out->dL_dopacity || !out->dL_dmeans3D || !out->dL_dcov3D ||
+      !out->dL_dscales || !out->dL_drotations || !out->dL_dtau)
+    return PG_ERR_ARG;
+  if (g->shs && !out->dL_dsh) return PG_ERR_ARG;
+  const int gx = div_up(W, kTile), gy = div_up(H, kTile);
+  cudaStream_t st = (cudaStream_t)stream;
+  GeomWs gw;
+  BinWs bw;
+  ImageWs iw;
+  carve_geom(prm->variant, P, geom_ws, &gw);
+  carve_binning(num_rendered, binning_ws, &bw);
+  carve_image(prm->variant, W, H, image_ws, &iw);
+  PG_CUDA(cudaMemsetAsync(gw.gacc, 0, sizeof(float4) * 3 * (size_t)P, st));
+  PG_CUDA(cudaMemsetAsync(gw.tau_acc, 0, sizeof(double) * 8, st));
+  if (num_rendered > 0) {
+    const uint32_t* point_list = sorted_point_list(bw, W, H);
+    r3_render_bwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
+                                                        iw.final_T, iw.n_contrib, in->dL_dout_color,
+                                                        in->dL_dout_depth, gw.gacc);
+    PG_LAUNCH_CHECK(prm->debug, st);
+  }
+  R3BwdPreArgs a;
+  a.P = P; a.D = prm->sh_degree; a.M = prm->sh_coeffs; a.W = W; a.H = H;
+  a.means = g->means3D; a.scales = g->scales; a.rots = g->rotations; a.shs = g->shs; a.cov3D_pre = g->cov3D_precomp;
+  a.view = prm->viewmatrix; a.proj = prm->projmatrix; a.proj_raw = prm->projmatrix_raw; a.campos = prm->campos;
+  a.radii = in->radii; a.clamped = gw.clamped; a.gacc = gw.gacc;
+  a.mod = prm->scale_modifier; a.tanx = prm->tanfovx; a.tany = prm->tanfovy;
+  a.fx = W / (2.0f * prm->tanfovx);
+  a.fy = H / (2.0f * prm->tanfovy);
+  a.dL_dmeans2D = out->dL_dmeans2D; a.dL_dcolors = out->dL_dcolors; a.dL_dopacity = out->dL_dopacity;
+  a.dL_dmeans3D = out->dL_dmeans3D; a.dL_dcov3D = out->dL_dcov3D; a.dL_dsh = g->shs ? out->dL_dsh : nullptr;
+  a.dL_dscales = out->dL_dscales; a.dL_drots = out->dL_drotations;
+  a.dL_dtau_full = out->dL_dtau_full; a.tau_acc = gw.tau_acc; a.dL_dtau = out->dL_dtau;
+  r3_preprocess_bwd_kernel<<<div_up(P, 256), 256, 0, st>>>(a);
+  PG_LAUNCH_CHECK(prm->debug, st);
+  return PG_OK;
+}
+
+int pg_raster_debug_views(int variant, int P, int width, int height, int64_t num_rendered, void* geom_ws,
+                          void* binning_ws, void* image_ws, const uint32_t** point_list, const uint32_t** ranges,
+                          const float** final_T, const uint32_t** n_contrib, const float** records,
+                          const uint32_t** depth_sorted_idx) {
+  GeomWs gw;
+  BinWs bw;
+  ImageWs iw;
+  carve_geom(variant, P, geom_ws, &gw);
+  carve_binning(num_rendered, binning_ws, &bw);
+  carve_image(variant, width, height, image_ws, &iw);
+  if (point_list) *point_list = sorted_point_list(bw, width, height);
+  if (ranges) *ranges = reinterpret_cast<const uint32_t*>(iw.ranges);
+  if (final_T) *final_T = iw.final_T;
+  if (n_contrib) *n_contrib = iw.n_contrib;
+  if (records) *records = reinterpret_cast<const float*>(gw.rec);
+  if (depth_sorted_idx) *depth_sorted_idx = gw.sorted_idx;
+  return PG_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,275 @@
+// CUB-free device primitives: exclusive scan (u32) and a stable LSD radix-sort pass
+// (hist -> scan -> scatter) for (key, u32 value) pairs.  Replaces the reference's
+// cub::DeviceScan::InclusiveSum / cub::DeviceRadixSort::SortPairs call sites
+// (R3 cuda_rasterizer/rasterizer_impl.cu:280,306-311).
+//
+// Design notes (B200): all kernels are pure HBM streams; a block owns a contiguous chunk of
+// 4096 items (256 threads x 16), loads are 32-lane coalesced, ranking inside a warp uses
+// MATCH.ANY so equal digits cost one shared-memory update per distinct digit (tile keys
+// arrive in long equal runs, so plain shared atomics would serialise).
+#pragma once
+#include "pg_common.cuh"
+
+namespace pg {
+
+constexpr int kScanThreads = 256;
+constexpr int kScanIpt = 16;
+constexpr int kScanChunk = kScanThreads * kScanIpt;  // 4096
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, int lane) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
+  }
+  return v;
+}
+
+// Block-wide exclusive scan of one value per thread (256 threads). Returns exclusive prefix,
+// writes block total to *total (all threads receive it).
+__device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* total) {
+  __shared__ uint32_t wsum[8];
+  __shared__ uint32_t tot;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t inc = warp_incl_scan(v, lane);
+  if (lane == 31) wsum[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = lane < 8 ? wsum[lane] : 0u;
+    uint32_t wi = warp_incl_scan(w, lane);
+    if (lane < 8) wsum[lane] = wi - w;
+    if (lane == 7) tot = wi;
+  }
+  __syncthreads();
+  uint32_t r = inc - v + wsum[warp];
+  *total = tot;
+  __syncthreads();
+  return r;
+}
+
+// ---- scan: level 1 reduce ------------------------------------------------------------------
+template <bool GATHER>
+__global__ void __launch_bounds__(kScanThreads) scan_reduce_kernel(
+    const uint32_t* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t n,
+    uint32_t* __restrict__ block_sums) {
+  const uint32_t base = blockIdx.x * kScanChunk;
+  uint32_t s = 0;
+#pragma unroll
+  for (int k = 0; k < kScanIpt; ++k) {
+    uint32_t i = base + k * kScanThreads + threadIdx.x;
+    if (i < n) s += GATHER ? in[idx[i]] : in[i];
+  }
+  __shared__ uint32_t red[8];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t t = 0;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    block_sums[blockIdx.x] = t;
+  }
+}
+
+// ---- scan: level 2, single block, exclusive in place ---------------------------------------
+__global__ void __launch_bounds__(1024) scan_sums_kernel(uint32_t* __restrict__ sums, uint32_t m,
+                                                          uint32_t* __restrict__ total_out) {
+  __shared__ uint32_t wsum[32];
+  __shared__ uint32_t carry_s;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (uint32_t base = 0; base < m; base += 1024) {
+    uint32_t i = base + threadIdx.x;
+    uint32_t v = i < m ? sums[i] : 0u;
+    uint32_t inc = warp_incl_scan(v, lane);
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      uint32_t w = wsum[lane];
+      uint32_t wi = warp_incl_scan(w, lane);
+      wsum[lane] = wi - w;
+    }
+    __syncthreads();
+    uint32_t carry = carry_s;
+    uint32_t ex = inc - v + wsum[warp] + carry;
+    if (i < m) sums[i] = ex;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry_s = ex + v;
+    __syncthreads();
+  }
+  if (total_out && threadIdx.x == 0) *total_out = carry_s;
+}
+
+// ---- scan: level 1 downsweep (exclusive) ----------------------------------------------------
+template <bool GATHER>
+__global__ void __launch_bounds__(kScanThreads) scan_down_kernel(
+    const uint32_t* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t n,
+    const uint32_t* __restrict__ block_sums, uint32_t* __restrict__ out) {
+  // thread t owns items [base + t*16, base + t*16 + 16)
+  const uint32_t base = blockIdx.x * kScanChunk + threadIdx.x * kScanIpt;
+  uint32_t v[kScanIpt];
+  uint32_t s = 0;
+#pragma unroll
+  for (int k = 0; k < kScanIpt; ++k) {
+    uint32_t i = base + k;
+    uint32_t x = 0;
+    if (i < n) x = GATHER ? in[idx[i]] : in[i];
+    v[k] = s;
+    s += x;
+  }
+  uint32_t tot;
+  uint32_t ex = block_excl_scan_256(s, &tot) + block_sums[blockIdx.x];
+#pragma unroll
+  for (int k = 0; k < kScanIpt; ++k) {
+    uint32_t i = base + k;
+    if (i < n) out[i] = v[k] + ex;
+  }
+}
+
+inline size_t scan_scratch_elems(size_t n) { return (n + kScanChunk - 1) / kScanChunk + 1; }
+
+// Exclusive scan of n u32 (optionally gathered through idx). `scratch` holds
+// scan_scratch_elems(n) u32. If total_out != nullptr the grand total is written there.
+// in == out is allowed when idx == nullptr.
+inline cudaError_t exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, uint32_t n,
+                                      uint32_t* out, uint32_t* scratch, uint32_t* total_out,
+                                      cudaStream_t st) {
+  if (n == 0) {
+    if (total_out) return cudaMemsetAsync(total_out, 0, sizeof(uint32_t), st);
+    return cudaSuccess;
+  }
+  const uint32_t nblk = (n + kScanChunk - 1) / kScanChunk;
+  if (idx) scan_reduce_kernel<true><<<nblk, kScanThreads, 0, st>>>(in, idx, n, scratch);
+  else     scan_reduce_kernel<false><<<nblk, kScanThreads, 0, st>>>(in, idx, n, scratch);
+  scan_sums_kernel<<<1, 1024, 0, st>>>(scratch, nblk, total_out);
+  if (idx) scan_down_kernel<true><<<nblk, kScanThreads, 0, st>>>(in, idx, n, scratch, out);
+  else     scan_down_kernel<false><<<nblk, kScanThreads, 0, st>>>(in, idx, n, scratch, out);
+  return cudaGetLastError();
+}
+
+// ---- radix pass ---------------------------------------------------------------------------
+constexpr int kSortThreads = 256;
+constexpr int kSortWarps = 8;
+constexpr int kSortIpt = 16;
+constexpr int kSortChunk = kSortThreads * kSortIpt;  // 4096
+constexpr int kSortWarpItems = 32 * kSortIpt;         // 512
+
+// hist[d * nblk + blk] = number of items of block `blk` with digit d.
+template <typename KeyT>
+__global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(
+    const KeyT* __restrict__ keys, uint32_t n, int shift, uint32_t nbins,
+    uint32_t* __restrict__ hist, uint32_t nblk) {
+  __shared__ uint32_t h[256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t base = blockIdx.x * kSortChunk + warp * kSortWarpItems;
+  const uint32_t mask = nbins - 1;
+  uint32_t d[kSortIpt];
+#pragma unroll
+  for (int it = 0; it < kSortIpt; ++it) {
+    uint32_t i = base + it * 32 + lane;
+    d[it] = i < n ? ((uint32_t)(keys[i] >> shift) & mask) : 0xffffffffu;
+  }
+#pragma unroll
+  for (int it = 0; it < kSortIpt; ++it) {
+    uint32_t peers = __match_any_sync(0xffffffffu, d[it]);
+    if (d[it] != 0xffffffffu && lane == (__ffs(peers) - 1)) atomicAdd(&h[d[it]], __popc(peers));
+  }
+  __syncthreads();
+  if (threadIdx.x < nbins) hist[threadIdx.x * nblk + blockIdx.x] = h[threadIdx.x];
+}
+
+// Stable scatter. `offs` is the exclusive scan of the digit-major histogram matrix.
+// IOTA: values are generated as the item index (first pass of an argsort).
+template <typename KeyT, bool IOTA, bool WRITE_KEYS>
+__global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(
+    const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin, KeyT* __restrict__ kout,
+    uint32_t* __restrict__ vout, uint32_t n, int shift, uint32_t nbins,
+    const uint32_t* __restrict__ offs, uint32_t nblk) {
+  __shared__ uint32_t wh[kSortWarps][256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int w = 0; w < kSortWarps; ++w) wh[w][threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t base = blockIdx.x * kSortChunk + warp * kSortWarpItems;
+  const uint32_t mask = nbins - 1;
+  KeyT k[kSortIpt];
+  uint32_t v[kSortIpt];
+#pragma unroll
+  for (int it = 0; it < kSortIpt; ++it) {
+    uint32_t i = base + it * 32 + lane;
+    if (i < n) {
+      k[it] = kin[i];
+      v[it] = IOTA ? i : vin[i];
+    } else {
+      k[it] = 0;
+      v[it] = 0;
+    }
+  }
+  // per-warp digit counts
+#pragma unroll
+  for (int it = 0; it < kSortIpt; ++it) {
+    uint32_t i = base + it * 32 + lane;
+    uint32_t d = i < n ? ((uint32_t)(k[it] >> shift) & mask) : 0xffffffffu;
+    uint32_t peers = __match_any_sync(0xffffffffu, d);
+    if (d != 0xffffffffu && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
+    __syncwarp();
+  }
+  __syncthreads();
+  // digit = threadIdx.x: turn counts into starting offsets (global base + earlier warps)
+  if (threadIdx.x < nbins) {
+    uint32_t run = offs[threadIdx.x * nblk + blockIdx.x];
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) {
+      uint32_t c = wh[w][threadIdx.x];
+      wh[w][threadIdx.x] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+  const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+  for (int it = 0; it < kSortIpt; ++it) {
+    uint32_t i = base + it * 32 + lane;
+    bool valid = i < n;
+    uint32_t d = valid ? ((uint32_t)(k[it] >> shift) & mask) : 0xffffffffu;
+    uint32_t peers = __match_any_sync(0xffffffffu, d);
+    uint32_t pos = 0;
+    if (valid) {
+      pos = wh[warp][d] + __popc(peers & lt);
+      if (WRITE_KEYS) kout[pos] = k[it];
+      vout[pos] = v[it];
+    }
+    __syncwarp();
+    if (valid && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
+    __syncwarp();
+  }
+}
+
+inline uint32_t sort_num_blocks(uint64_t n) { return (uint32_t)((n + kSortChunk - 1) / kSortChunk); }
+// u32 elements of scratch needed by one radix pass over n items (hist matrix + scan scratch).
+inline size_t sort_scratch_elems(uint64_t n) {
+  size_t hm = (size_t)sort_num_blocks(n) * 256;
+  return hm + scan_scratch_elems(hm) + 64;
+}
+
+// One stable pass on bits [shift, shift+bits) (bits <= 8).
+template <typename KeyT, bool IOTA, bool WRITE_KEYS>
+inline cudaError_t radix_pass(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout,
+                              uint32_t n, int shift, int bits, uint32_t* scratch, cudaStream_t st) {
+  if (n == 0) return cudaSuccess;
+  const uint32_t nblk = sort_num_blocks(n);
+  const uint32_t nbins = 1u << bits;
+  uint32_t* hist = scratch;
+  uint32_t* scan_scratch = scratch + (size_t)nblk * 256;
+  radix_hist_kernel<KeyT><<<nblk, kSortThreads, 0, st>>>(kin, n, shift, nbins, hist, nblk);
+  cudaError_t e = exclusive_scan_u32(hist, nullptr, nbins * nblk, hist, scan_scratch, nullptr, st);
+  if (e != cudaSuccess) return e;
+  radix_scatter_kernel<KeyT, IOTA, WRITE_KEYS><<<nblk, kSortThreads, 0, st>>>(
+      kin, vin, kout, vout, n, shift, nbins, hist, nblk);
+  return cudaGetLastError();
+}
+
+}  // namespace pg
