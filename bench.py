@@ -1,0 +1,414 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the pings_b200 hot path (contract in the task statement).
+
+Workload at every N (BASELINE.json configs[1]): 3DGS rasterizer forward +
+backward with camera-pose gradients, 500,000 synthetic Gaussians, one 1226x370 KITTI-shaped
+view per step per GPU.  metric = raster fwd+bwd Mpix/s (whole job).  A "step" = one view:
+preprocess -> depth sort -> binning -> blend -> blend backward -> per-Gaussian backward
+(+ NCCL all-reduce of the Gaussian-parameter gradients when N > 1, the training exchange step).
+
+  value : inputs resident in HBM, CUDA events around each step (L2 flushed between steps).
+  e2e   : the same step through the reference-facing API (GaussianRasterizer autograd module)
+          with HOST (pinned) Gaussian parameters: H2D copies, forward, L1+depth loss, backward,
+          D2H of loss + pose gradient inside the timed region.
+  roofline : dominant kernel (by device time, measured with CUDA events on the launching stream
+          via the library's phase timer), algorithmic bytes of SURVEY.md §8d / DESIGN.md.
+  cpu_baseline : oracle/ CPU restatement timed on this box's host cores on a bounded sample.
+  extra.sdf : the second half of the metric (SDF queries/s, config C1) when that path is built.
+
+`--impl reference` times the UNMODIFIED reference CUDA rasterizer (oracle/_ref/libref_r3.so, built
+from /root/reference's own sources) on the same scene; the reference has no CPU rasterizer, so that
+is its only implementation of this path.  If that library is absent the
+arm falls back to the CPU restatement.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+C2 = dict(P=500_000, W=1226, H=370, seed=0)
+
+
+# ----------------------------------------------------------------------------------------------
+def peaks() -> dict:
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm_gbs=float(d["hbm_gbs"]), source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm_gbs=6650.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines: list[str] = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._pump, daemon=True)
+            self.thr.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return dict(sm_mhz=statistics.median(sm) if sm else None, sm_max_mhz=max(smax) if smax else None,
+                    samples=len(sm), reasons=sorted(reasons))
+
+
+def dist_setup(n_gpus: int):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    else:
+        torch.cuda.set_device(0)
+    return rank, world, local
+
+
+def barrier(world):
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+# ----------------------------------------------------------------------------------------------
+def make_scene(rank: int):
+    """C2 scene; every rank sees the same Gaussians from its own seeded pose (view sharding)."""
+    from pings_b200 import synth
+    cam0 = synth.kitti_camera(C2["seed"], C2["W"], C2["H"])
+    sc = synth.gaussians_in_view(cam0, C2["P"], C2["seed"])
+    cam = cam0
+    if rank > 0:  # other ranks: a nearby pose along a 4 m path (SURVEY.md §8d C4 style)
+        T = cam0.T_wc.clone()
+        T[:3, 3] += T[:3, 2] * (0.5 * rank)
+        cam = synth.Camera(cam0.W, cam0.H, cam0.fx, cam0.fy, cam0.cx, cam0.cy, T)
+    ct = synth.cotangents(cam, C2["seed"])
+    g = torch.Generator().manual_seed(77)
+    target = torch.rand(3, C2["H"], C2["W"], generator=g)
+    return cam, sc, ct, target
+
+
+def algorithmic_bytes(P: int, R: int, W: int, H: int) -> dict:
+    """Per-launch algorithmic HBM bytes of each phase."""
+    WH = W * H
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    return {
+        "preprocess_fwd": 104 * P,                    # 44 B in + 60 B out per Gaussian
+        "depth_sort": (4 * (4 + 8 + 8) + 4) * P,      # 4 LSD passes over (u32 key, u32 value) + histogram read
+        "binning": 20 * P + 6 * R + 2 * (2 * R + 12 * R) + 2 * R + 8 * T,  # emit + 2 tile passes (hist+scatter) + ranges
+        "render_fwd": 52 * R + 28 * WH,               # id 4 B + 48-B record per instance; 28 B per pixel out
+        "render_bwd": 52 * R + 2 * 48 * R + 24 * WH,  # + 48-B gradient record RMW per (tile, Gaussian)
+        "preprocess_bwd": 190 * P,
+    }
+
+
+def launches_per_step(T: int) -> int:
+    """Kernel launches of one fwd+bwd (radix pass = hist + 3 scan + scatter)."""
+    scan = 3
+    rp = 1 + scan + 1
+    tile_passes = 2 if T > 256 else 1
+    return 1 + 4 * rp + scan + 1 + tile_passes * rp + 1 + 1 + 1 + 1
+
+
+def run_ours(args, rank, world, local):
+    from pings_b200 import _lib as L, _raster_c as RC
+    from pings_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    dev = torch.device("cuda", local)
+    cam, sc_cpu, ct_cpu, target_cpu = make_scene(rank)
+    P, W, H = C2["P"], C2["W"], C2["H"]
+    sc = {k: v.to(dev) for k, v in sc_cpu.items()}
+    ct = {k: v.to(dev) for k, v in ct_cpu.items()}
+    view, full, proj, center = [m.to(dev) for m in cam.matrices()]
+    bg = torch.ones(3, device=dev)
+    e = torch.empty(0)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    grads_flat = torch.zeros(P * 14, device=dev)
+
+    def step_resident():
+        R, color, radii, geom, binning, img, depth, opac, n_touched = RC.rasterize_gaussians(
+            bg, sc["means3D"], sc["colors_precomp"], sc["opacities"], sc["scales"], sc["rotations"], 1.0, e, view, full,
+            proj, cam.tanfovx, cam.tanfovy, H, W, e, 0, center, False, False)
+        out = RC.rasterize_gaussians_backward(bg, sc["means3D"], radii, sc["colors_precomp"], sc["scales"],
+                                              sc["rotations"], 1.0, e, view, full, proj, cam.tanfovx, cam.tanfovy,
+                                              ct["color"], ct["depth"], e, 0, center, geom, R, binning, img, False)
+        if world > 1:
+            # training exchange step: sum the Gaussian-parameter gradients over the view shards
+            torch.cat([out[3].flatten(), out[1].flatten(), out[2].flatten(), out[6].flatten(), out[7].flatten()],
+                      out=grads_flat)
+            dist.all_reduce(grads_flat)
+        return R
+
+    # ---- warm-up + timed region (device-resident) ----
+    for _ in range(args.warmup):
+        R = step_resident()
+    barrier(world)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    evs = []
+    for _ in range(args.steps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        R = step_resident()
+        b.record()
+        evs.append((a, b))
+    barrier(world)
+    clocks = sampler.stop() if rank == 0 else None
+    ms_total = sum(a.elapsed_time(b) for a, b in evs)
+    t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    ms_per_step = ms_total / args.steps
+    value = world * W * H / (ms_per_step * 1e-3) / 1e6
+
+    # ---- e2e through the public API with host buffers ----
+    pinned = {k: v.contiguous().pin_memory() for k, v in sc_cpu.items()}
+    target = target_cpu.to(dev)
+    h2d_bytes = sum(v.numel() * v.element_size() for v in pinned.values())
+    host_out = torch.empty(7, dtype=torch.float32).pin_memory()
+    rs = GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, bg, 1.0, view, full, proj, 0, center, False, False)
+    rast = GaussianRasterizer(rs)
+
+    def step_e2e():
+        leaves = {k: pinned[k].to(dev, non_blocking=True).requires_grad_(True) for k in pinned}
+        theta = torch.zeros(1, 3, device=dev, requires_grad=True)
+        rho = torch.zeros(1, 3, device=dev, requires_grad=True)
+        m2d = torch.zeros(P, 3, device=dev, requires_grad=True)
+        color, radii, depth, opacity, n_touched = rast(leaves["means3D"], m2d, leaves["opacities"],
+                                                       colors_precomp=leaves["colors_precomp"], scales=leaves["scales"],
+                                                       rotations=leaves["rotations"], theta=theta, rho=rho)
+        loss = (color - target).abs().mean() + 0.01 * depth.mean()
+        loss.backward()
+        if world > 1:
+            torch.cat([leaves[k].grad.flatten() for k in ("means3D", "colors_precomp", "opacities", "scales", "rotations")],
+                      out=grads_flat)
+            dist.all_reduce(grads_flat)
+        res = torch.cat([loss.detach().view(1), rho.grad.flatten(), theta.grad.flatten()])
+        host_out.copy_(res, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return float(host_out[0])
+
+    for _ in range(args.warmup):
+        step_e2e()
+    barrier(world)
+    e2e_ms = 0.0
+    for _ in range(args.steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        step_e2e()
+        e2e_ms += (time.perf_counter() - t0) * 1e3
+    t = torch.tensor([e2e_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms_per_step = float(t.item()) / args.steps
+    e2e_value = world * W * H / (e2e_ms_per_step * 1e-3) / 1e6
+
+    # ---- per-phase attribution (separate pass; events on the launching stream) ----
+    phases: dict[str, list[float]] = {}
+    if rank == 0:
+        L.timing_enable(True)
+        for _ in range(3):
+            flush.fill_(1)
+            step_resident()
+            for name, ms in L.timing_drain():
+                phases.setdefault(name, []).append(ms)
+        L.timing_enable(False)
+    barrier(world)
+    if rank != 0:
+        return None
+    phase_ms = {k: sum(v) / len(v) for k, v in phases.items()}
+    ab = algorithmic_bytes(P, R, W, H)
+    pk = peaks()
+    dom = max(phase_ms, key=phase_ms.get)
+    achieved = ab[dom] / (phase_ms[dom] * 1e-3) / 1e9
+    per_phase = {k: dict(ms=round(phase_ms[k], 4), alg_bytes=ab[k],
+                         gbs=round(ab[k] / (phase_ms[k] * 1e-3) / 1e9, 1),
+                         frac=round(ab[k] / (phase_ms[k] * 1e-3) / 1e9 / pk["hbm_gbs"], 4)) for k in phase_ms}
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    line = {
+        "metric": "raster fwd+bwd Mpix/s (3DGS, pose grads)", "value": round(value, 2), "unit": "Mpix/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C2: 3DGS rasterizer fwd+bwd with pose grads, 500k synthetic Gaussians, one 1226x370 view "
+                               "per GPU per step (BASELINE.json configs[1])",
+                   "P": P, "W": W, "H": H, "num_rendered": int(R), "views_per_step": world,
+                   "l2": "flushed between steps (256 MiB write)",
+                   "exchange": "NCCL all-reduce of Gaussian-parameter grads (28 MB)" if world > 1 else "none (N=1)"},
+        "clocks": clocks,
+        "e2e": {"value": round(e2e_value, 2), "unit": "Mpix/s", "ms_per_step": round(e2e_ms_per_step, 4),
+                "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 28},
+        "gpu_launches": launches_per_step(T) * args.steps,
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": pk["hbm_gbs"],
+                     "unit": "GB/s", "frac": round(achieved / pk["hbm_gbs"], 4), "traffic": TRAFFIC.get(dom),
+                     "peak_source": pk["source"], "phases": per_phase},
+    }
+    return line
+
+
+# per-launch dram bytes of the dominant kernels from profiles/ (ncu --set full), filled in as captured
+TRAFFIC: dict = {}
+
+
+def cpu_baseline_line(args) -> dict | None:
+    try:
+        from oracle import cpu_raster
+    except ImportError:
+        return None
+    return cpu_raster.bench_sample(C2, seconds_budget=20.0)
+
+
+def run_reference(args, rank, world, local):
+    """The unmodified reference CUDA rasterizer on the same scene (rank 0 only)."""
+    if rank != 0:
+        return None
+    from oracle import ref_api
+    P, W, H = C2["P"], C2["W"], C2["H"]
+    if not ref_api.available("ref_r3"):
+        cb = cpu_baseline_line(args)
+        if cb is None:
+            return {"impl": "reference", "unavailable": "oracle/_ref/libref_r3.so and oracle CPU port both missing"}
+        return {"impl": "reference", "metric": "raster fwd+bwd Mpix/s (3DGS, pose grads)", "value": cb["value"],
+                "unit": "Mpix/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "higher_is_better": True, "cpu_baseline": cb,
+                "e2e": {"value": cb["value"], "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    dev = torch.device("cuda", local)
+    cam, sc_cpu, ct_cpu, _ = make_scene(0)
+    sc = {k: v.to(dev) for k, v in sc_cpu.items()}
+    ct = {k: v.to(dev) for k, v in ct_cpu.items()}
+    view, full, proj, center = [m.to(dev) for m in cam.matrices()]
+    bg = torch.ones(3, device=dev)
+    ref = ref_api.RefRaster3()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step():
+        r = ref.forward(sc, (view, full, proj), W, H, cam.tanfovx, cam.tanfovy, bg, campos=center, want_views=False)
+        g = ref.backward(sc, (view, full, proj), cam.tanfovx, cam.tanfovy, bg, r["radii"], ct["color"], ct["depth"],
+                         campos=center)
+        tau = g["tau"].sum(0)  # R3 diff_gaussian_rasterization/__init__.py:152
+        return r["num_rendered"], tau
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms = 0.0
+    for _ in range(args.steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        R, tau = step()
+        torch.cuda.synchronize()
+        ms += (time.perf_counter() - t0) * 1e3
+    clocks = sampler.stop()
+    ms_per_step = ms / args.steps
+    value = W * H / (ms_per_step * 1e-3) / 1e6
+    return {"impl": "reference", "metric": "raster fwd+bwd Mpix/s (3DGS, pose grads)", "value": round(value, 2),
+            "unit": "Mpix/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": round(ms_per_step, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C2: 3DGS rasterizer fwd+bwd with pose grads, 500k synthetic Gaussians, one 1226x370 view",
+                       "P": P, "W": W, "H": H, "num_rendered": int(R),
+                       "note": "reference = unmodified submodules/diff-gaussian-rasterization-w-pose CUDA sources "
+                               "compiled for sm_100a (oracle/_ref/libref_r3.so) on this GPU; the reference has no CPU "
+                               "rasterizer. Host wall-clock around fwd+bwd (+ its torch.sum of dL_dtau), device synced."},
+            "clocks": clocks,
+            "cpu_baseline": {"value": round(value, 2), "unit": "Mpix/s", "cores": 0, "kind": "reference",
+                             "sample": "full C2 view per step, reference CUDA kernels on the same B200 (no CPU "
+                                       "implementation of this path exists in the reference)"},
+            "e2e": {"value": round(value, 2), "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":  # rank 0 alone runs it; no process group is formed
+        if int(os.environ.get("RANK", "0")) == 0:
+            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+            world = int(os.environ.get("WORLD_SIZE", "1"))
+            print(json.dumps(run_reference(args, 0, world, int(os.environ.get("LOCAL_RANK", "0")))), flush=True)
+        return
+    rank, world, local = dist_setup(args.gpus)
+    line = run_ours(args, rank, world, local)
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            cb = cpu_baseline_line(args)
+            if cb is not None:
+                line["cpu_baseline"] = cb
+        for extra in EXTRAS:
+            try:
+                line.setdefault("extra", {}).update(extra(args, local))
+            except Exception as ex:  # an optional leg must not take the headline down
+                line.setdefault("extra", {})[getattr(extra, "__name__", "extra")] = f"failed: {ex!r}"
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+EXTRAS: list = []
+
+if __name__ == "__main__":
+    main()

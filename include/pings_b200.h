@@ -36,6 +36,13 @@ int pg_abi_version(void);
 /* Last CUDA error string recorded by this library on the calling thread ("" if none). */
 const char* pg_last_error(void);
 
+/* Opt-in per-phase device timing (no reference counterpart; the reference only has host
+ * wall-clock timers, utils/tools.py:551-558).  When enabled on the calling thread every group of
+ * launches is bracketed by a CUDA-event pair on the launching stream; pg_timing_drain() waits for
+ * them and returns (static) phase names + milliseconds in launch order. */
+int pg_timing_enable(int on);
+int pg_timing_drain(int max_phases, const char** names, float* ms);
+
 /* ------------------------------------------------------------------------------------------
  * Rasterizer (3DGS: R3/rasterize_points.h:18-39,41-65,67-70; surfel: RS/rasterize_points.cu:36-60,134-162)
  * ---------------------------------------------------------------------------------------- */

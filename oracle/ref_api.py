@@ -57,7 +57,7 @@ class RefRaster3:
             pass
 
     def forward(self, scene: dict, cam_mats, W, H, tanx, tany, bg, mod=1.0, sh=None, degree=0, campos=None,
-                cov3D=None):
+                cov3D=None, want_views=True):
         """scene tensors must be CUDA fp32 contiguous. Returns dict of outputs + internal views."""
         torch.cuda.synchronize()
         view, proj, proj_raw = cam_mats
@@ -82,7 +82,8 @@ class RefRaster3:
         self.P, self.W, self.H, self.R = P, W, H, R
         res = dict(num_rendered=R, color=out_color, depth=out_depth, opacity=out_opacity, radii=radii,
                    n_touched=n_touched)
-        res.update(self.views())
+        if want_views:
+            res.update(self.views())
         return res
 
     def views(self) -> dict:

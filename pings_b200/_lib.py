@@ -69,6 +69,10 @@ def lib() -> C.CDLL:
     L = C.CDLL(LIB_PATH)
     L.pg_abi_version.restype = C.c_int
     L.pg_last_error.restype = C.c_char_p
+    L.pg_timing_enable.restype = C.c_int
+    L.pg_timing_enable.argtypes = [C.c_int]
+    L.pg_timing_drain.restype = C.c_int
+    L.pg_timing_drain.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(C.c_float)]
     L.pg_raster_geom_bytes.restype = C.c_size_t
     L.pg_raster_geom_bytes.argtypes = [C.c_int, C.c_int]
     L.pg_raster_image_bytes.restype = C.c_size_t
@@ -103,6 +107,20 @@ def _declare_optional(L: C.CDLL) -> None:
 
 
 OPTIONAL_SIGNATURES: dict = {}
+
+
+def timing_enable(on: bool) -> None:
+    lib().pg_timing_enable(int(on))
+
+
+def timing_drain(max_phases: int = 4096) -> list[tuple[str, float]]:
+    """[(phase name, ms)] recorded on this thread since the last drain (synchronises on the events)."""
+    names = (C.c_char_p * max_phases)()
+    ms = (C.c_float * max_phases)()
+    n = lib().pg_timing_drain(max_phases, names, ms)
+    if n < 0:
+        raise RuntimeError("pings_b200: timing drain failed")
+    return [(names[i].decode(), float(ms[i])) for i in range(n)]
 
 
 def check(rc: int, what: str) -> None:

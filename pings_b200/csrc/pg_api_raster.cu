@@ -2,8 +2,6 @@
 #include "pg_raster3_bwd.cuh"
 
 namespace pg {
-thread_local char g_last_error[256] = {0};
-
 struct HostSlot {
   unsigned long long* pinned = nullptr;
   cudaEvent_t ev = nullptr;
@@ -38,9 +36,6 @@ static bool params_ok(const PgRasterParams* p) {
 using namespace pg;
 
 extern "C" {
-
-int pg_abi_version(void) { return 1; }
-const char* pg_last_error(void) { return g_last_error; }
 
 size_t pg_raster_geom_bytes(int variant, int P) { return carve_geom(variant, P, nullptr, nullptr); }
 size_t pg_raster_image_bytes(int variant, int width, int height) {
@@ -93,13 +88,19 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
   a.fx = W / (2.0f * prm->tanfovx);
   a.fy = H / (2.0f * prm->tanfovy);
   a.prefiltered = prm->prefiltered;
-  r3_preprocess_kernel<<<div_up(P, 256), 256, 0, st>>>(a, radii, ws.rec, ws.dkey, ws.tiles, ws.rect, ws.clamped,
-                                                      ws.total);
+  {
+    Phase ph("preprocess_fwd", st);
+    r3_preprocess_kernel<<<div_up(P, 256), 256, 0, st>>>(a, radii, ws.rec, ws.dkey, ws.tiles, ws.rect, ws.clamped,
+                                                        ws.total);
+  }
   PG_LAUNCH_CHECK(prm->debug, st);
   PG_CUDA(cudaMemcpyAsync(g_slot.pinned, ws.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
   PG_CUDA(cudaEventRecord(g_slot.ev, st));
   // depth ordering runs while the host waits for the count
-  PG_CUDA(depth_order_and_offsets(ws, P, st));
+  {
+    Phase ph("depth_sort", st);
+    PG_CUDA(depth_order_and_offsets(ws, P, st));
+  }
   PG_LAUNCH_CHECK(prm->debug, st);
   PG_CUDA(cudaEventSynchronize(g_slot.ev));
   const unsigned long long R = *g_slot.pinned;
@@ -128,11 +129,17 @@ int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, vo
   carve_binning(num_rendered, binning_ws, &bw);
   carve_image(prm->variant, W, H, image_ws, &iw);
   const uint32_t* point_list = nullptr;
-  PG_CUDA(bin_instances(gw, bw, iw, P, W, H, num_rendered, &point_list, st));
+  {
+    Phase ph("binning", st);
+    PG_CUDA(bin_instances(gw, bw, iw, P, W, H, num_rendered, &point_list, st));
+  }
   PG_LAUNCH_CHECK(prm->debug, st);
-  r3_render_fwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
-                                                      out->out_color, out->out_depth, out->out_opacity, iw.final_T,
-                                                      iw.n_contrib, out->n_touched);
+  {
+    Phase ph("render_fwd", st);
+    r3_render_fwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
+                                                        out->out_color, out->out_depth, out->out_opacity, iw.final_T,
+                                                        iw.n_contrib, out->n_touched);
+  }
   PG_LAUNCH_CHECK(prm->debug, st);
   return PG_OK;
 }
@@ -165,6 +172,7 @@ int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g, void* ge
   PG_CUDA(cudaMemsetAsync(gw.tau_acc, 0, sizeof(double) * 8, st));
   if (num_rendered > 0) {
     const uint32_t* point_list = sorted_point_list(bw, W, H);
+    Phase ph("render_bwd", st);
     r3_render_bwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
                                                         iw.final_T, iw.n_contrib, in->dL_dout_color,
                                                         in->dL_dout_depth, gw.gacc);
@@ -182,7 +190,10 @@ int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g, void* ge
   a.dL_dmeans3D = out->dL_dmeans3D; a.dL_dcov3D = out->dL_dcov3D; a.dL_dsh = g->shs ? out->dL_dsh : nullptr;
   a.dL_dscales = out->dL_dscales; a.dL_drots = out->dL_drotations;
   a.dL_dtau_full = out->dL_dtau_full; a.tau_acc = gw.tau_acc; a.dL_dtau = out->dL_dtau;
-  r3_preprocess_bwd_kernel<<<div_up(P, 256), 256, 0, st>>>(a);
+  {
+    Phase ph("preprocess_bwd", st);
+    r3_preprocess_bwd_kernel<<<div_up(P, 256), 256, 0, st>>>(a);
+  }
   PG_LAUNCH_CHECK(prm->debug, st);
   return PG_OK;
 }

@@ -37,6 +37,16 @@ inline int record_cuda_error(cudaError_t e, const char* what, int line) {
     }                                                                         \
   } while (0)
 
+// Opt-in phase timer (pg_api_core.cu): records a CUDA-event pair around a group of launches.
+bool timing_on();
+void phase_begin(const char* name, cudaStream_t st);
+void phase_end(cudaStream_t st);
+struct Phase {
+  cudaStream_t st;
+  Phase(const char* name, cudaStream_t s) : st(s) { phase_begin(name, s); }
+  ~Phase() { phase_end(st); }
+};
+
 constexpr int kSmCount = 148;  // B200: 2 dies x 74 SMs
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
