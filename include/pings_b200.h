@@ -151,6 +151,106 @@ int pg_raster_debug_views(int variant, int P, int width, int height, int64_t num
                           const float** final_T, const uint32_t** n_contrib,
                           const float** records /* float4[3P] */, const uint32_t** depth_sorted_idx);
 
+
+/* ------------------------------------------------------------------------------------------
+ * Neural-point map: voxel-hash kNN, top-k + inverse-distance interpolation, decoder MLP
+ * (NP = model/neural_gaussians.py, DEC = model/decoder.py, utils/mapper.py:2273-2289).
+ * The reference implements these as chains of eager torch ops; there is no native symbol to
+ * replace, so the entry points mirror the Python methods one-to-one.
+ * ---------------------------------------------------------------------------------------- */
+
+/* The global map + search neighbourhood read by NeuralPoints.radius_neighborhood_search (NP:1061-1115). */
+typedef struct PgNeuralMap {
+  int64_t buffer_size;              /* config.buffer_size (NP:52) */
+  const int64_t* buffer_pt_index;   /* [buffer_size] int64 slot table, -1 = empty (NP:86-88) */
+  const float* neural_points;       /* [n_points,3] */
+  int64_t n_points;
+  const int64_t* neighbor_dx;       /* [K,3] cell offsets (NP:1026-1059) */
+  int32_t K;
+  int64_t primes[3];                /* NP:80-82 */
+  float resolution;                 /* voxel_size_m */
+  float max_valid_dist2;            /* 3((n+1) res)^2 rounded to fp32 */
+  const int32_t* point_ts_create;   /* [n_points]; only read when time filtering is on (NP:1088-1094) */
+  const float* travel_dist;         /* [n_ts] */
+  int32_t cur_ts;
+  float diff_travel_dist_local;
+} PgNeuralMap;
+
+/* radius_neighborhood_search: dist2 [N,K] f32 and idx [N,K] i64 exactly as NP:1061-1115 returns them. */
+int pg_np_radius_search(const PgNeuralMap* map, int64_t N, const float* query_xyz, int time_filtering,
+                        float* out_dist2, int64_t* out_idx, void* stream);
+
+/* Arguments of NeuralPoints.query_feature (NP:506-725). `points/orientations/certainties/*_features`
+ * are the arrays indexed by the FINAL index: the local map when query_locally != 0, else the global one. */
+typedef struct PgQueryArgs {
+  int32_t nn_k;
+  int32_t time_filtering;
+  int32_t query_locally;
+  int32_t use_only_measured;        /* mask free_gs_mask (NP:544-546) */
+  int32_t use_only_valid;           /* mask ~valid_gs_mask (NP:548-550) */
+  int32_t weighted_first;           /* config.weighted_first (NP:701-710) */
+  int32_t after_pgo;                /* rotate neighbour vectors by the point orientation (NP:627-630) */
+  int32_t F_geo, F_color;           /* feature widths; 0 = not queried */
+  const uint8_t* free_gs_mask;      /* [n_points] */
+  const uint8_t* valid_gs_mask;     /* [n_points] */
+  const int64_t* global2local;      /* [n_points+1] (NP:455-466) */
+  const float* points;              /* [n,3] */
+  const float* orientations;        /* [n,4] (w,x,y,z) */
+  const float* certainties;         /* [n] */
+  const float* geo_features;        /* [n+1,F_geo] */
+  const float* color_features;      /* [n+1,F_color] */
+} PgQueryArgs;
+
+typedef struct PgQueryOut {
+  float* geo_vec;      /* [N,F_geo+3] if weighted_first else [N,nn_k,F_geo+3]; NULL if F_geo == 0 */
+  float* color_vec;    /* same with F_color */
+  float* weight;       /* [N,nn_k] */
+  int64_t* nn_counts;  /* [N] counted before the top-k cut (NP:557-558) */
+  float* certainty;    /* [N] */
+  int32_t* knn_idx;    /* [N,nn_k] final index of each kept neighbour, -1 = invalid */
+  float* knn_dist2;    /* [N,nn_k] sorted ascending, 9e3 for invalid slots (NP:562) */
+} PgQueryOut;
+
+int pg_np_query_feature(const PgNeuralMap* map, const PgQueryArgs* args, int64_t N, const float* query_xyz,
+                        const PgQueryOut* out, void* stream);
+
+/* Side effects of query_feature(accumulate_stability=True) (NP:664-689): certainties scatter_add and
+ * ts_update amax.  Run after pg_np_query_feature on the same stream. query_ts may be NULL. */
+int pg_np_accumulate_stability(int64_t N, int32_t nn_k, const int32_t* knn_idx, const float* weight,
+                               const int32_t* query_ts, float* certainties, int32_t* ts_update, void* stream);
+
+/* Backward of query_feature w.r.t. the feature tables and the query coordinates (autograd of NP:506-725:
+ * through the gathered features, the neighbour vectors and the IDW weights).  d_*_features are
+ * ACCUMULATED into (caller zero-fills); d_query [N,3] is overwritten; any of them may be NULL. */
+int pg_np_query_feature_backward(const PgQueryArgs* args, int64_t N, const float* query_xyz,
+                                 const int32_t* knn_idx, const float* knn_dist2, const float* weight,
+                                 const int64_t* nn_counts, const float* d_geo_vec, const float* d_color_vec,
+                                 const float* d_weight, float* d_geo_features, float* d_color_features,
+                                 float* d_query, void* stream);
+
+/* Decoder MLP (DEC:14-104): hidden_level x (Linear + ReLU | LeakyReLU(0.01)) + Linear.
+ * weights[l] is nn.Linear.weight ([out,in] row-major), biases[l] may be NULL (mlp_bias_on = False). */
+#define PG_MLP_MAX_LAYERS 6
+typedef struct PgMlp {
+  int32_t in_dim, hidden_dim, hidden_level, out_dim;
+  int32_t leaky_relu;
+  const float* weights[PG_MLP_MAX_LAYERS];
+  const float* biases[PG_MLP_MAX_LAYERS];
+} PgMlp;
+
+/* y[N,out_dim] = mlp(x[N,in_dim]).  hidden_save (optional) receives the post-activation hidden
+ * states [hidden_level][N,hidden_dim] needed by the backward. */
+int pg_mlp_forward(const PgMlp* mlp, int64_t N, const float* x, float* y, float* hidden_save, void* stream);
+/* dX (optional) overwritten; dW[l], dB[l] ACCUMULATED into (caller zero-fills); dB[l] may be NULL. */
+int pg_mlp_backward(const PgMlp* mlp, int64_t N, const float* x, const float* hidden_save, const float* dY,
+                    float* dX, float* const* dW, float* const* dB, void* stream);
+
+/* Fused inference SDF query = Mapper.sdf under no_grad (utils/mapper.py:2273-2289):
+ * kNN -> top-k -> IDW -> decoder -> sdf * sdf_scale (-> weighted mean over k if !weighted_first).
+ * sdf_std (optional, !weighted_first only) as utils/mapper.py:2280-2284. */
+int pg_sdf_query(const PgNeuralMap* map, const PgQueryArgs* args, const PgMlp* mlp, float sdf_scale, int64_t N,
+                 const float* query_xyz, float* sdf, float* sdf_std, int64_t* nn_counts, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

