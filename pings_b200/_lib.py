@@ -51,6 +51,34 @@ class PgRasterBwdOut(C.Structure):
                 ("dL_dtau_full", fp)]
 
 
+PG_MLP_MAX_LAYERS = 6
+
+
+class PgNeuralMap(C.Structure):
+    _fields_ = [("buffer_size", C.c_int64), ("buffer_pt_index", fp), ("neural_points", fp), ("n_points", C.c_int64),
+                ("neighbor_dx", fp), ("K", C.c_int32), ("primes", C.c_int64 * 3), ("resolution", C.c_float),
+                ("max_valid_dist2", C.c_float), ("point_ts_create", fp), ("travel_dist", fp), ("cur_ts", C.c_int32),
+                ("diff_travel_dist_local", C.c_float)]
+
+
+class PgQueryArgs(C.Structure):
+    _fields_ = [("nn_k", C.c_int32), ("time_filtering", C.c_int32), ("query_locally", C.c_int32),
+                ("use_only_measured", C.c_int32), ("use_only_valid", C.c_int32), ("weighted_first", C.c_int32),
+                ("after_pgo", C.c_int32), ("F_geo", C.c_int32), ("F_color", C.c_int32),
+                ("free_gs_mask", fp), ("valid_gs_mask", fp), ("global2local", fp), ("points", fp),
+                ("orientations", fp), ("certainties", fp), ("geo_features", fp), ("color_features", fp)]
+
+
+class PgQueryOut(C.Structure):
+    _fields_ = [("geo_vec", fp), ("color_vec", fp), ("weight", fp), ("nn_counts", fp), ("certainty", fp),
+                ("knn_idx", fp), ("knn_dist2", fp)]
+
+
+class PgMlp(C.Structure):
+    _fields_ = [("in_dim", C.c_int32), ("hidden_dim", C.c_int32), ("hidden_level", C.c_int32), ("out_dim", C.c_int32),
+                ("leaky_relu", C.c_int32), ("weights", fp * PG_MLP_MAX_LAYERS), ("biases", fp * PG_MLP_MAX_LAYERS)]
+
+
 class PingsB200LibraryMissing(ImportError):
     pass
 
@@ -92,6 +120,22 @@ def lib() -> C.CDLL:
                                      C.POINTER(PgRasterBwdIn), C.POINTER(PgRasterBwdOut), fp]
     L.pg_raster_debug_views.restype = C.c_int
     L.pg_raster_debug_views.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, fp, fp, fp] + [C.POINTER(fp)] * 6
+    L.pg_np_radius_search.restype = C.c_int
+    L.pg_np_radius_search.argtypes = [C.POINTER(PgNeuralMap), C.c_int64, fp, C.c_int, fp, fp, fp]
+    L.pg_np_query_feature.restype = C.c_int
+    L.pg_np_query_feature.argtypes = [C.POINTER(PgNeuralMap), C.POINTER(PgQueryArgs), C.c_int64, fp,
+                                      C.POINTER(PgQueryOut), fp]
+    L.pg_np_accumulate_stability.restype = C.c_int
+    L.pg_np_accumulate_stability.argtypes = [C.c_int64, C.c_int32, fp, fp, fp, fp, fp, fp]
+    L.pg_np_query_feature_backward.restype = C.c_int
+    L.pg_np_query_feature_backward.argtypes = [C.POINTER(PgQueryArgs), C.c_int64] + [fp] * 12
+    L.pg_mlp_forward.restype = C.c_int
+    L.pg_mlp_forward.argtypes = [C.POINTER(PgMlp), C.c_int64, fp, fp, fp, fp]
+    L.pg_mlp_backward.restype = C.c_int
+    L.pg_mlp_backward.argtypes = [C.POINTER(PgMlp), C.c_int64, fp, fp, fp, fp, C.POINTER(fp), C.POINTER(fp), fp]
+    L.pg_sdf_query.restype = C.c_int
+    L.pg_sdf_query.argtypes = [C.POINTER(PgNeuralMap), C.POINTER(PgQueryArgs), C.POINTER(PgMlp), C.c_float, C.c_int64,
+                               fp, fp, fp, fp, fp]
     _declare_optional(L)
     _lib = L
     return L

@@ -1,0 +1,226 @@
+// C-ABI entry points of the neural-point path (see include/pings_b200.h).
+#include "pg_sdf.cuh"
+
+using namespace pg;
+
+namespace {
+
+bool map_ok(const PgNeuralMap* m, bool tf) {
+  if (!m || m->buffer_size <= 0 || !m->buffer_pt_index || !m->neural_points || m->n_points <= 0) return false;
+  if (!m->neighbor_dx || m->K <= 0 || m->K > 256 || !(m->resolution > 0.f)) return false;
+  if (tf && (!m->point_ts_create || !m->travel_dist)) return false;
+  return true;
+}
+
+NpMapDev to_dev(const PgNeuralMap* m, int time_filtering) {
+  NpMapDev d;
+  d.buffer_size = m->buffer_size;
+  d.table = reinterpret_cast<const long long*>(m->buffer_pt_index);
+  d.pts = m->neural_points;
+  d.n_points = m->n_points;
+  d.dx = reinterpret_cast<const long long*>(m->neighbor_dx);
+  d.K = m->K;
+  d.p0 = m->primes[0]; d.p1 = m->primes[1]; d.p2 = m->primes[2];
+  d.res = m->resolution;
+  d.max_valid = m->max_valid_dist2;
+  d.ts_create = m->point_ts_create;
+  d.travel = m->travel_dist;
+  d.cur_ts = m->cur_ts;
+  d.diff_local = m->diff_travel_dist_local;
+  d.time_filtering = time_filtering;
+  return d;
+}
+
+bool query_ok(const PgQueryArgs* a) {
+  if (!a || a->nn_k <= 0 || a->nn_k > kNpMaxK) return false;
+  if (a->F_geo < 0 || a->F_color < 0 || (a->F_geo == 0 && a->F_color == 0)) return false;
+  if (!a->points || (a->F_geo && !a->geo_features) || (a->F_color && !a->color_features)) return false;
+  if (a->use_only_measured && !a->free_gs_mask) return false;
+  if (a->use_only_valid && !a->valid_gs_mask) return false;
+  if (a->query_locally && !a->global2local) return false;
+  if (a->after_pgo && !a->orientations) return false;
+  return true;
+}
+
+NpQueryDev to_dev(const PgQueryArgs* a) {
+  NpQueryDev d;
+  d.nn_k = a->nn_k; d.query_locally = a->query_locally; d.use_only_measured = a->use_only_measured;
+  d.use_only_valid = a->use_only_valid; d.weighted_first = a->weighted_first; d.after_pgo = a->after_pgo;
+  d.F_geo = a->F_geo; d.F_color = a->F_color;
+  d.free_mask = a->free_gs_mask; d.valid_mask = a->valid_gs_mask;
+  d.g2l = reinterpret_cast<const long long*>(a->global2local);
+  d.points = a->points; d.quats = a->orientations; d.cert = a->certainties;
+  d.geo = a->geo_features; d.color = a->color_features;
+  return d;
+}
+
+bool mlp_ok(const PgMlp* m) {
+  if (!m || m->in_dim <= 0 || m->hidden_dim <= 0 || m->out_dim <= 0) return false;
+  if (m->hidden_level < 1 || m->hidden_level + 1 > PG_MLP_MAX_LAYERS) return false;
+  for (int l = 0; l <= m->hidden_level; ++l)
+    if (!m->weights[l]) return false;
+  return true;
+}
+
+MlpDev to_dev(const PgMlp* m) {
+  MlpDev d;
+  d.in_dim = m->in_dim; d.hidden = m->hidden_dim; d.levels = m->hidden_level; d.out_dim = m->out_dim;
+  d.leaky = m->leaky_relu;
+  for (int l = 0; l < PG_MLP_MAX_LAYERS; ++l) {
+    d.W[l] = l <= m->hidden_level ? m->weights[l] : nullptr;
+    d.B[l] = l <= m->hidden_level ? m->biases[l] : nullptr;
+  }
+  return d;
+}
+
+constexpr size_t kMaxDynSmem = 227 * 1024;
+
+template <typename F>
+int with_cpl(int K, F&& f) {
+  if (K <= 32) return f(std::integral_constant<int, 1>{});
+  if (K <= 96) return f(std::integral_constant<int, 3>{});
+  if (K <= 128) return f(std::integral_constant<int, 4>{});
+  return f(std::integral_constant<int, 8>{});
+}
+
+}  // namespace
+
+extern "C" {
+
+int pg_np_radius_search(const PgNeuralMap* map, int64_t N, const float* q, int time_filtering, float* out_dist2,
+                        int64_t* out_idx, void* stream) {
+  if (N < 0 || !map_ok(map, time_filtering != 0)) return PG_ERR_ARG;
+  if (N == 0) return PG_OK;
+  if (!q || !out_dist2 || !out_idx) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long total = (long long)N * map->K;
+  const long long blocks = (total + 255) / 256;
+  if (blocks > 0x7fffffffLL) return PG_ERR_UNSUPPORTED;
+  Phase ph("np_radius_search", st);
+  np_radius_search_kernel<<<(unsigned)blocks, 256, 0, st>>>(to_dev(map, time_filtering), N, q, out_dist2,
+                                                          reinterpret_cast<long long*>(out_idx));
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_np_query_feature(const PgNeuralMap* map, const PgQueryArgs* args, int64_t N, const float* q,
+                        const PgQueryOut* out, void* stream) {
+  if (N < 0 || !query_ok(args) || !map_ok(map, args->time_filtering != 0) || !out) return PG_ERR_ARG;
+  if (N == 0) return PG_OK;
+  if (!q || !out->weight || !out->nn_counts) return PG_ERR_ARG;
+  if (out->certainty && !args->certainties) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long blocks = (N + kNpWarps - 1) / kNpWarps;
+  if (blocks > 0x7fffffffLL) return PG_ERR_UNSUPPORTED;
+  const NpMapDev m = to_dev(map, args->time_filtering);
+  const NpQueryDev a = to_dev(args);
+  float* geo = args->F_geo ? out->geo_vec : nullptr;
+  float* col = args->F_color ? out->color_vec : nullptr;
+  Phase ph("np_query_feature", st);
+  return with_cpl(map->K, [&](auto cpl) {
+    np_query_kernel<decltype(cpl)::value><<<(unsigned)blocks, kNpWarps * 32, 0, st>>>(
+        m, a, N, q, geo, col, out->weight, reinterpret_cast<long long*>(out->nn_counts), out->certainty, out->knn_idx,
+        out->knn_dist2);
+    PG_LAUNCH_CHECK(0, st);
+    return PG_OK;
+  });
+}
+
+int pg_np_accumulate_stability(int64_t N, int32_t nn_k, const int32_t* knn_idx, const float* weight,
+                               const int32_t* query_ts, float* certainties, int32_t* ts_update, void* stream) {
+  if (N < 0 || nn_k <= 0) return PG_ERR_ARG;
+  if (N == 0) return PG_OK;
+  if (!knn_idx || !weight || !certainties) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long total = (long long)N * nn_k;
+  Phase ph("np_accumulate", st);
+  np_accumulate_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(total, nn_k, knn_idx, weight, query_ts,
+                                                                      certainties, ts_update);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_np_query_feature_backward(const PgQueryArgs* args, int64_t N, const float* q, const int32_t* knn_idx,
+                                 const float* knn_dist2, const float* weight, const int64_t* nn_counts,
+                                 const float* d_geo_vec, const float* d_color_vec, const float* d_weight,
+                                 float* d_geo_features, float* d_color_features, float* d_query, void* stream) {
+  if (N < 0 || !query_ok(args)) return PG_ERR_ARG;
+  if (N == 0) return PG_OK;
+  if (!q || !knn_idx || !knn_dist2 || !weight || !nn_counts) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long blocks = (N + kNpWarps - 1) / kNpWarps;
+  Phase ph("np_query_feature_bwd", st);
+  np_query_bwd_kernel<<<(unsigned)blocks, kNpWarps * 32, 0, st>>>(
+      to_dev(args), N, q, knn_idx, knn_dist2, weight, reinterpret_cast<const long long*>(nn_counts),
+      args->F_geo ? d_geo_vec : nullptr, args->F_color ? d_color_vec : nullptr, d_weight, d_geo_features,
+      d_color_features, d_query);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_mlp_forward(const PgMlp* mlp, int64_t N, const float* x, float* y, float* hidden_save, void* stream) {
+  if (N < 0 || !mlp_ok(mlp)) return PG_ERR_ARG;
+  if (N == 0) return PG_OK;
+  if (!x || !y) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const MlpDev m = to_dev(mlp);
+  const size_t smem = mlp_smem_floats(m) * sizeof(float);
+  if (smem > kMaxDynSmem) return PG_ERR_UNSUPPORTED;
+  PG_CUDA(cudaFuncSetAttribute(mlp_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  Phase ph("mlp_forward", st);
+  mlp_forward_kernel<<<(unsigned)((N + kMlpRows - 1) / kMlpRows), kMlpThreads, smem, st>>>(m, N, x, y, hidden_save);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_mlp_backward(const PgMlp* mlp, int64_t N, const float* x, const float* hidden_save, const float* dY,
+                    float* dX, float* const* dW, float* const* dB, void* stream) {
+  if (N < 0 || !mlp_ok(mlp) || !dW) return PG_ERR_ARG;
+  if (N == 0) return PG_OK;
+  if (!x || !hidden_save || !dY) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const MlpDev m = to_dev(mlp);
+  MlpGradDev g;
+  for (int l = 0; l < PG_MLP_MAX_LAYERS; ++l) {
+    g.dW[l] = l <= m.levels ? dW[l] : nullptr;
+    g.dB[l] = (dB && l <= m.levels) ? dB[l] : nullptr;
+    if (l <= m.levels && !g.dW[l]) return PG_ERR_ARG;
+  }
+  const size_t smem = mlp_bwd_smem_floats(m) * sizeof(float);
+  if (smem > kMaxDynSmem) return PG_ERR_UNSUPPORTED;
+  PG_CUDA(cudaFuncSetAttribute(mlp_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  Phase ph("mlp_backward", st);
+  mlp_backward_kernel<<<(unsigned)((N + kMlpRows - 1) / kMlpRows), kMlpThreads, smem, st>>>(m, g, N, x, hidden_save, dY,
+                                                                                         dX);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_sdf_query(const PgNeuralMap* map, const PgQueryArgs* args, const PgMlp* mlp, float sdf_scale, int64_t N,
+                 const float* q, float* sdf, float* sdf_std, int64_t* nn_counts, void* stream) {
+  if (N < 0 || !query_ok(args) || !map_ok(map, args->time_filtering != 0) || !mlp_ok(mlp)) return PG_ERR_ARG;
+  if (args->F_geo <= 0 || mlp->in_dim != args->F_geo + 3 || mlp->out_dim != 1) return PG_ERR_ARG;
+  if (N == 0) return PG_OK;
+  if (!q || !sdf) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  const NpMapDev m = to_dev(map, args->time_filtering);
+  const NpQueryDev a = to_dev(args);
+  const MlpDev md = to_dev(mlp);
+  const size_t smem = sdf_smem_floats(md) * sizeof(float);
+  if (smem > kMaxDynSmem) return PG_ERR_UNSUPPORTED;
+  long long blocks = (N + kSdfWarps - 1) / kSdfWarps;
+  const long long cap = (long long)kSmCount * 8;  // persistent CTAs: weights are staged once per CTA
+  if (blocks > cap) blocks = cap;
+  Phase ph("sdf_query", st);
+  return with_cpl(map->K, [&](auto cpl) {
+    auto kern = sdf_query_kernel<decltype(cpl)::value>;
+    PG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)blocks, kSdfWarps * 32, smem, st>>>(m, a, md, sdf_scale, N, q, sdf,
+                                                         args->weighted_first ? nullptr : sdf_std,
+                                                         reinterpret_cast<long long*>(nn_counts));
+    PG_LAUNCH_CHECK(0, st);
+    return PG_OK;
+  });
+}
+
+}  // extern "C"

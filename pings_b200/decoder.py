@@ -1,0 +1,132 @@
+"""Mirror of the reference's Decoder (model/decoder.py:14-135): same constructor arguments, same
+parameter layout (`layers.{i}.weight/bias`, `lout.weight/bias`, so reference state_dicts load
+unchanged), same methods — with the MLP evaluated by the fused sm_100a kernels behind the C-ABI
+(pg_mlp_forward / pg_mlp_backward) instead of a cuBLAS sgemm + activation kernel per layer.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import _lib as L
+
+
+class _MlpFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, dec, x, *params):
+        lib = L.lib()
+        if not x.is_cuda:
+            raise RuntimeError("pings_b200.Decoder: expected CUDA tensors (there is no CPU fallback)")
+        lead = x.shape[:-1]
+        x2 = x.detach().reshape(-1, x.shape[-1]).to(torch.float32).contiguous()
+        N, dev = x2.shape[0], x2.device
+        mlp, keep = dec._mlp_struct()
+        y = torch.empty(N, dec.mlp_out_dim, dtype=torch.float32, device=dev)
+        need = any(ctx.needs_input_grad[1:])
+        hs = torch.empty(dec.hidden_level, N, dec.hidden_dim, dtype=torch.float32, device=dev) if need else None
+        with torch.cuda.device(dev):
+            L.check(lib.pg_mlp_forward(C.byref(mlp), N, x2.data_ptr(), y.data_ptr(), L.ptr(hs),
+                                       torch.cuda.current_stream(dev).cuda_stream), "mlp forward")
+        if need:
+            ctx.dec, ctx.lead = dec, lead
+            ctx.save_for_backward(x2, hs)
+        return y.reshape(*lead, dec.mlp_out_dim)
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = L.lib()
+        dec = ctx.dec
+        x2, hs = ctx.saved_tensors
+        N, dev = x2.shape[0], x2.device
+        dy2 = dy.reshape(N, dec.mlp_out_dim).to(torch.float32).contiguous()
+        mlp, keep = dec._mlp_struct()
+        lin = dec._linears()
+        dWs = [torch.zeros_like(l.weight, dtype=torch.float32) for l in lin]
+        dBs = [torch.zeros_like(l.bias, dtype=torch.float32) if l.bias is not None else None for l in lin]
+        dX = torch.empty_like(x2) if ctx.needs_input_grad[1] else None
+        pw = (L.fp * len(lin))(*[t.data_ptr() for t in dWs])
+        pb = (L.fp * len(lin))(*[None if t is None else t.data_ptr() for t in dBs])
+        with torch.cuda.device(dev):
+            L.check(lib.pg_mlp_backward(C.byref(mlp), N, x2.data_ptr(), hs.data_ptr(), dy2.data_ptr(), L.ptr(dX), pw, pb,
+                                        torch.cuda.current_stream(dev).cuda_stream), "mlp backward")
+        grads = []
+        for w, b in zip(dWs, dBs):
+            grads.append(w)
+            if b is not None:
+                grads.append(b)
+        return (None, None if dX is None else dX.reshape(*ctx.lead, x2.shape[1]), *grads)
+
+
+class Decoder(nn.Module):
+    def __init__(self, config, input_feature_dim, hidden_dim, hidden_level, out_dim, out_k=1, pos_dim=3,
+                 is_time_conditioned=False):
+        super().__init__()
+        self.mlp_out_dim = out_dim * out_k
+        self.out_dim_per = out_dim
+        self.out_k = out_k
+        self.use_leaky_relu = config.mlp_leaky_relu
+        self.bs = config.infer_bs
+        self.hidden_dim, self.hidden_level = hidden_dim, hidden_level
+        bias_on = config.mlp_bias_on
+        input_dim = input_feature_dim + pos_dim + (1 if is_time_conditioned else 0)
+        self.input_dim = input_dim
+        self.layers = nn.ModuleList([nn.Linear(input_dim if i == 0 else hidden_dim, hidden_dim, bias_on)
+                                     for i in range(hidden_level)])
+        self.lout = nn.Linear(hidden_dim, self.mlp_out_dim, bias_on)
+        self.sdf_scale = 1.0
+        if config.main_loss_type == "bce":
+            self.sdf_scale = config.logistic_gaussian_ratio * config.sigma_sigmoid_m
+        self.to(config.device)
+
+    def _linears(self):
+        return list(self.layers) + [self.lout]
+
+    def _mlp_struct(self):
+        m = L.PgMlp()
+        m.in_dim, m.hidden_dim, m.hidden_level, m.out_dim = self.input_dim, self.hidden_dim, self.hidden_level, self.mlp_out_dim
+        m.leaky_relu = int(bool(self.use_leaky_relu))
+        keep = []
+        for i, lin in enumerate(self._linears()):
+            w = lin.weight.detach().contiguous()
+            keep.append(w)
+            m.weights[i] = w.data_ptr()
+            if lin.bias is not None:
+                b = lin.bias.detach().contiguous()
+                keep.append(b)
+                m.biases[i] = b.data_ptr()
+        self._keep = keep
+        return m, keep
+
+    def _params(self):
+        ps = []
+        for lin in self._linears():
+            ps.append(lin.weight)
+            if lin.bias is not None:
+                ps.append(lin.bias)
+        return ps
+
+    def mlp(self, features):
+        """DEC:62-82."""
+        return _MlpFn.apply(self, features, *self._params())
+
+    def mlp_batch(self, features):
+        """DEC:84-98. One fused launch covers any row count, so no infer_bs chunking is needed."""
+        return self.mlp(features)
+
+    def sdf(self, features):
+        return self.mlp(features).squeeze(1) * self.sdf_scale
+
+    def occupancy(self, features):
+        return torch.sigmoid(self.sdf(features) / -self.sdf_scale)
+
+    def sem_label_prob(self, features):
+        return F.log_softmax(self.mlp(features), dim=-1)
+
+    def sem_label(self, features):
+        return torch.argmax(self.sem_label_prob(features), dim=1)
+
+    def regress_color(self, features):
+        return torch.sigmoid(self.mlp(features))

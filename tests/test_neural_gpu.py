@@ -1,0 +1,126 @@
+"""GPU parity of the neural-point kernels (through the C-ABI + the Python mirror) against
+(a) golden vectors produced by the reference itself (tests/golden/neural_*.npz) and
+(b) the CPU oracle (oracle/neural_cpu.py) on larger seeded inputs.
+kNN index lists / nn_counts bit-exact; dist2 bit-exact; interpolated features, weights, SDF and all
+gradients within rtol 1e-4 / atol 1e-6 (fp32 summation order differs from torch's)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import neural_cpu as O
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+CASES = ["pin", "gs", "window"]
+RTOL, ATOL = 1e-4, 2e-6
+
+
+def build(name):
+    from pings_b200.decoder import Decoder
+    from pings_b200.neural_points import NeuralPoints, default_config
+    z = np.load(os.path.join(GOLD, f"neural_{name}.npz"))
+    m = z["meta"]
+    cfg = default_config(voxel_size_m=float(m[0]), num_nei_cells=int(m[1]), search_alpha=float(m[2]), query_nn_k=int(m[3]),
+                         buffer_size=int(m[4]), feature_dim=int(m[5]), color_feature_dim=int(m[6]), color_on=int(m[6]) > 0,
+                         weighted_first=bool(m[9]))
+    state = {k[6:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("state.")}
+    npm = NeuralPoints.from_state(cfg, state)
+    npm.after_pgo = bool(m[10])
+    npm.cur_ts = int(m[11])
+    npm.diff_travel_dist_local = float(m[12])
+    npm.temporal_local_map_on = bool(m[13])
+    dec = Decoder(cfg, int(m[5]), int(m[7]), int(m[8]), 1)
+    dec.load_state_dict({k[4:]: torch.from_numpy(z[k]) for k in z.files if k.startswith("dec.")})
+    dec.sdf_scale = float(m[17])
+    return z, m, npm, dec.cuda()
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_radius_search_bitexact(name):
+    z, m, npm, dec = build(name)
+    d2, idx = npm.radius_neighborhood_search(torch.from_numpy(z["q"]).cuda(), time_filtering=bool(m[13]))
+    assert np.array_equal(idx.cpu().numpy().astype(np.int32), z["idx"])
+    assert np.array_equal(d2.cpu().numpy(), z["dist2"])
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_query_feature_sdf_and_gradients(name):
+    z, m, npm, dec = build(name)
+    wf, color_q = bool(m[9]), bool(m[14])
+    q = torch.from_numpy(z["q"]).cuda().requires_grad_(True)
+    q_ts = torch.from_numpy(z["q_ts"]).cuda()
+    geo_vec, color_vec, weight, nn_counts, certainty = npm.query_feature(
+        q, q_ts, accumulate_stability=True, query_color_feature=color_q, use_only_valid_points=bool(m[15]),
+        use_only_measured_points=bool(m[16]))
+    assert np.array_equal(nn_counts.cpu().numpy(), z["nn_counts"])
+    c = lambda t: t.detach().cpu().numpy()
+    np.testing.assert_allclose(c(weight), z["weight"], rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(c(geo_vec), z["geo_vec"], rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(c(certainty), z["certainty"], rtol=RTOL, atol=ATOL)
+    np.testing.assert_allclose(c(npm.local_point_certainties), z["cert_after"], rtol=RTOL, atol=1e-5)
+    assert np.array_equal(c(npm.local_point_ts_update), z["ts_after"])
+    sdf = dec.sdf(geo_vec)
+    if not wf:
+        sdf = torch.sum(sdf * weight, dim=1).squeeze(1)
+    np.testing.assert_allclose(c(sdf), z["sdf"], rtol=RTOL, atol=ATOL)
+    loss = (sdf * torch.from_numpy(z["r1"]).cuda()).sum() + (weight * torch.from_numpy(z["r2"]).cuda()).sum()
+    if color_q:
+        np.testing.assert_allclose(c(color_vec), z["color_vec"], rtol=RTOL, atol=ATOL)
+        loss = loss + (color_vec * torch.from_numpy(z["r3"]).cuda()).sum()
+    loss.backward()
+
+    def close(a, b, what):
+        scale = np.abs(b).max() + 1e-30
+        assert np.abs(a - b).max() / scale < 2e-4, (what, np.abs(a - b).max(), scale)
+
+    close(c(npm.local_geo_features.grad), z["d_geo"], "d_geo")
+    close(c(q.grad), z["d_q"], "d_q")
+    if color_q:
+        close(c(npm.local_color_features.grad), z["d_color"], "d_color")
+    for k, p in dec.named_parameters():
+        close(c(p.grad), z[f"dgrad.{k}"], k)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_fused_sdf_query_matches(name):
+    z, m, npm, dec = build(name)
+    sdf, std, cnt = npm.sdf_fused(torch.from_numpy(z["q"]).cuda(), dec, get_std=True,
+                                  use_only_valid_points=bool(m[15]), use_only_measured_points=bool(m[16]))
+    assert np.array_equal(cnt.cpu().numpy(), z["nn_counts"])
+    np.testing.assert_allclose(sdf.cpu().numpy(), z["sdf"], rtol=RTOL, atol=ATOL)
+    if std is not None:
+        S = O.state_from_golden(z)
+        nl = int(m[8])
+        Ws = [torch.from_numpy(z[f"dec.layers.{i}.weight"]) for i in range(nl)] + [torch.from_numpy(z["dec.lout.weight"])]
+        Bs = [torch.from_numpy(z[f"dec.layers.{i}.bias"]) for i in range(nl)] + [torch.from_numpy(z["dec.lout.bias"])]
+        _, std_ref, _ = O.sdf_query(S, torch.from_numpy(z["q"]), int(m[3]), False, Ws, Bs, float(m[17]),
+                                    time_filtering=bool(m[13]), use_only_valid=bool(m[15]), use_only_measured=bool(m[16]),
+                                    after_pgo=bool(m[10]))
+        np.testing.assert_allclose(std.cpu().numpy(), std_ref.numpy(), rtol=1e-3, atol=1e-5)
+
+
+def test_large_scan_vs_oracle_and_properties():
+    """C1-shaped inputs (64x1800 synthetic scan) against the CPU oracle + size-independent properties:
+    weights sum to 1 where any neighbour exists, nn_counts == #(idx >= 0), queries are independent (a
+    permutation of the queries permutes the outputs)."""
+    from pings_b200 import synth_neural as SN
+    npm, dec, q = SN.c1_map_and_queries(device="cuda", n_az=600)
+    S = SN.oracle_state(npm)
+    qc = q.cpu()
+    d2, idx = npm.radius_neighborhood_search(q, time_filtering=False)
+    d2o, idxo = O.radius_search(S, qc, False)
+    assert torch.equal(idx.cpu(), idxo) and torch.equal(d2.cpu(), d2o)
+    sdf, _, cnt = npm.sdf_fused(q, dec)
+    Ws, Bs = [l.weight.detach().cpu() for l in dec._linears()], [l.bias.detach().cpu() for l in dec._linears()]
+    so, _, co = O.sdf_query(S, qc, 6, True, Ws, Bs, dec.sdf_scale, time_filtering=False)
+    assert torch.equal(cnt.cpu(), co)
+    np.testing.assert_allclose(sdf.cpu().numpy(), so.numpy(), rtol=RTOL, atol=ATOL)
+    geo, _, w, cnt2, _ = npm.query_feature(q, accumulate_stability=False)
+    ws = w.sum(1).squeeze(-1)
+    assert torch.allclose(ws[cnt2 > 0], torch.ones_like(ws[cnt2 > 0]), atol=1e-5)
+    assert float(ws[cnt2 == 0].abs().sum()) == 0.0
+    perm = torch.randperm(q.shape[0], device="cuda")
+    sdf_p, _, _ = npm.sdf_fused(q[perm], dec)
+    assert torch.equal(sdf_p, sdf[perm])
