@@ -375,6 +375,112 @@ def run_reference(args, rank, world, local):
             "e2e": {"value": round(value, 2), "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 
+
+# ----------------------------------------------------------------------------------------------
+# Second half of the metric: SDF queries/s (config C1: one synthetic 64x1800 scan, PIN-SLAM settings)
+def sdf_leg(args, local, world=1, rank=0) -> dict:
+    from pings_b200 import _lib as L, synth_neural as SN
+    dev = torch.device("cuda", local)
+    npm, dec, q = SN.c1_map_and_queries(device=dev)
+    if rank > 0:  # query sharding: every rank holds the replicated map and takes its own scan-shaped batch
+        g = torch.Generator().manual_seed(1000 + rank)
+        q = (q.cpu() + 0.05 * torch.randn(q.shape, generator=g)).to(dev)
+    N = q.shape[0]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    steps, warm = max(args.steps, 10), max(args.warmup, 3)
+    for _ in range(warm):
+        npm.sdf_fused(q, dec)
+    barrier(world)
+    evs = []
+    for _ in range(steps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        npm.sdf_fused(q, dec)
+        b.record()
+        evs.append((a, b))
+    barrier(world)
+    ms = sum(a.elapsed_time(b) for a, b in evs) / steps
+    # e2e: host queries -> H2D -> fused query -> D2H of the sdf values
+    qh = q.cpu().pin_memory()
+    out_h = torch.empty(N, dtype=torch.float32).pin_memory()
+    def e2e():
+        qd = qh.to(dev, non_blocking=True)
+        sdf, _, cnt = npm.sdf_fused(qd, dec)
+        out_h.copy_(sdf, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    for _ in range(warm):
+        e2e()
+    t_e2e = 0.0
+    for _ in range(steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        e2e()
+        t_e2e += time.perf_counter() - t0
+    e2e_ms = t_e2e * 1e3 / steps
+    # training-shaped batch (bs = 10,000, run_pin_slam.yaml:24): query_feature + decoder + backward
+    qb = q[:10000].clone()
+    r = torch.randn(10000, device=dev)
+    def train_step():
+        npm.local_geo_features.grad = None
+        geo, _, w, cnt, _ = npm.query_feature(qb, accumulate_stability=False)
+        (dec.sdf(geo) * r).sum().backward()
+    for _ in range(warm):
+        train_step()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        train_step()
+    b.record()
+    torch.cuda.synchronize()
+    train_ms = a.elapsed_time(b) / steps
+    t = torch.tensor([ms, e2e_ms, train_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms, train_ms = [float(x) for x in t]
+    pk = peaks()
+    alg = N * (600 + 332 + 4 + 8)  # kNN 600 B + gather/IDW 332 B (int64 slot table kept: +0), + outputs
+    gbs = alg / (ms * 1e-3) / 1e9
+    return {"sdf": {"metric": "SDF queries/s (fused kNN+IDW+decoder, C1)", "value": round(world * N / (ms * 1e-3), 1),
+                    "unit": "queries/s", "ms_per_step": round(ms, 4), "queries_per_step_per_gpu": N,
+                    "neural_points": int(npm.count()), "slot_table": "int64[1e8] (800 MB, reference layout)",
+                    "e2e": {"value": round(world * N / (e2e_ms * 1e-3), 1), "unit": "queries/s",
+                            "h2d_bytes_per_step": N * 12, "d2h_bytes_per_step": N * 4},
+                    "train_fwd_bwd_bs10000": {"value": round(world * 10000 / (train_ms * 1e-3), 1), "unit": "queries/s",
+                                              "ms_per_step": round(train_ms, 4)},
+                    "roofline": {"bound": "hbm", "kernel": "sdf_query", "achieved": round(gbs, 1), "peak": pk["hbm_gbs"],
+                                 "unit": "GB/s", "frac": round(gbs / pk["hbm_gbs"], 4), "alg_bytes_per_query": 944,
+                                 "traffic": TRAFFIC.get("sdf_query")}}}
+
+
+def sdf_cpu_leg(budget_s: float = 15.0) -> dict:
+    """The reference's PyTorch CPU SDF path restated (oracle/neural_cpu.py) on this box's host cores."""
+    from oracle import neural_cpu as O
+    from pings_b200 import synth_neural as SN
+    torch.set_num_threads(os.cpu_count() or 1)
+    npm, dec, q = SN.c1_map_and_queries(device="cpu")
+    S = SN.oracle_state(npm)
+    Ws = [l.weight.detach() for l in dec._linears()]
+    Bs = [l.bias.detach() for l in dec._linears()]
+    def run():
+        with torch.no_grad():
+            for h in range(0, q.shape[0], 80000):  # infer_bs batches (config.py:774)
+                O.sdf_query(S, q[h:h + 80000], 6, True, Ws, Bs, dec.sdf_scale, time_filtering=False)
+    run()
+    times = []
+    t_end = time.perf_counter() + budget_s
+    while len(times) < 5 or (time.perf_counter() < t_end and len(times) < 20):
+        t0 = time.perf_counter()
+        run()
+        times.append(time.perf_counter() - t0)
+    best, med = min(times), statistics.median(times)
+    return {"value": round(q.shape[0] / med, 1), "best": round(q.shape[0] / best, 1), "unit": "queries/s",
+            "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"full C1 scan ({q.shape[0]} queries, infer_bs 80000, no_grad), median of {len(times)} runs"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -388,27 +494,33 @@ def main():
         if int(os.environ.get("RANK", "0")) == 0:
             torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
             world = int(os.environ.get("WORLD_SIZE", "1"))
-            print(json.dumps(run_reference(args, 0, world, int(os.environ.get("LOCAL_RANK", "0")))), flush=True)
+            ref_line = run_reference(args, 0, world, int(os.environ.get("LOCAL_RANK", "0")))
+            try:  # the reference's CPU SDF path (restated), the reported baseline of the second metric half
+                ref_line.setdefault("extra", {})["sdf"] = sdf_cpu_leg()
+            except Exception as ex:
+                ref_line.setdefault("extra", {})["sdf"] = f"failed: {ex!r}"
+            print(json.dumps(ref_line), flush=True)
         return
     rank, world, local = dist_setup(args.gpus)
     line = run_ours(args, rank, world, local)
+    try:  # every rank takes part (query sharding); an optional leg must not take the headline down
+        sdf = sdf_leg(args, local, world, rank)
+    except Exception as ex:
+        sdf = {"sdf": f"failed: {ex!r}"}
     if rank == 0:
+        line.setdefault("extra", {}).update(sdf)
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_baseline_line(args)
             if cb is not None:
                 line["cpu_baseline"] = cb
-        for extra in EXTRAS:
-            try:
-                line.setdefault("extra", {}).update(extra(args, local))
-            except Exception as ex:  # an optional leg must not take the headline down
-                line.setdefault("extra", {})[getattr(extra, "__name__", "extra")] = f"failed: {ex!r}"
+            if isinstance(line["extra"].get("sdf"), dict):
+                line["extra"]["sdf"]["cpu_baseline"] = sdf_cpu_leg()
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
-EXTRAS: list = []
 
 if __name__ == "__main__":
     main()
