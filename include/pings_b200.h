@@ -251,6 +251,18 @@ int pg_mlp_backward(const PgMlp* mlp, int64_t N, const float* x, const float* hi
 int pg_sdf_query(const PgNeuralMap* map, const PgQueryArgs* args, const PgMlp* mlp, float sdf_scale, int64_t N,
                  const float* query_xyz, float* sdf, float* sdf_std, int64_t* nn_counts, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Fused SSIM (FS/ssim.h:7-26: fusedssim, fusedssim_backward).  img*: [B,C,H,W] contiguous fp32.
+ * dm_* may be NULL in the forward (train == false, FS/ssim.cu:458-460).  In the backward dL_dmap
+ * may be NULL, in which case the map gradient is the constant dL_dmap_scalar (the backward of the
+ * `.mean()` in FS/fused_ssim/__init__.py:42) — one plane less to read.
+ * ---------------------------------------------------------------------------------------- */
+int pg_ssim_forward(int B, int C, int H, int W, float C1, float C2, const float* img1, const float* img2,
+                    float* ssim_map, float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12, void* stream);
+int pg_ssim_backward(int B, int C, int H, int W, float C1, float C2, const float* img1, const float* img2,
+                     const float* dL_dmap, float dL_dmap_scalar, const float* dm_dmu1, const float* dm_dsigma1_sq,
+                     const float* dm_dsigma12, float* dL_dimg1, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -44,19 +44,24 @@ def _build_raster(name: str, subdir: str, shim: str) -> str | None:
 
 
 def _build_ssim() -> str | None:
-    shim_path = os.path.join(HERE, "ref_ssim_capi.cu")
-    src = os.path.join(REF, "submodules", "fused-ssim", "ssim.cu")
-    if not (os.path.exists(src) and os.path.exists(shim_path)):
+    """The reference fused-ssim extension (ssim.cu + ext.cpp, torch C++ API) compiled in place as a
+    torch extension module `fused_ssim_cuda_ref` with the reference's own flags (-O3 --use_fast_math,
+    FS/setup.py:13-23) for sm_100a.  ~4 min once; cached by mtime."""
+    root = os.path.join(REF, "submodules", "fused-ssim")
+    srcs = [os.path.join(root, "ssim.cu"), os.path.join(root, "ext.cpp")]
+    if not all(os.path.exists(s) for s in srcs):
         return None
-    # ssim.cu includes torch/extension.h: build it as a torch extension-free object is not
-    # possible, so the SSIM reference is compiled through the shim which includes the kernel
-    # source text with the torch host part compiled out (see ref_ssim_capi.cu).
-    target = os.path.join(OUT, "libref_ssim.so")
-    if _newer(target, [src, shim_path]):
+    bdir = os.path.join(OUT, "fused_ssim_build")
+    target = os.path.join(OUT, "fused_ssim_cuda_ref.so")
+    if _newer(target, srcs):
         return target
-    cmd = [NVCC, "-std=c++17", "-O3", "--use_fast_math", *ARCH, "-I", os.path.dirname(src), "-shared", "-Xcompiler", "-fPIC", "-w",
-           "-o", target, shim_path]
-    subprocess.check_call(cmd)
+    os.makedirs(bdir, exist_ok=True)
+    os.environ.setdefault("TORCH_CUDA_ARCH_LIST", "10.0")
+    from torch.utils import cpp_extension
+    cpp_extension.load(name="fused_ssim_cuda_ref", sources=srcs, build_directory=bdir, is_python_module=False,
+                       extra_cflags=["-O3"], extra_cuda_cflags=["-O3", "--use_fast_math", *ARCH], verbose=False)
+    import shutil
+    shutil.copy(os.path.join(bdir, "fused_ssim_cuda_ref.so"), target)
     return target
 
 

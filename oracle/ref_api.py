@@ -137,3 +137,17 @@ class RefRaster3:
         present = torch.zeros(means.shape[0], dtype=torch.bool, device=means.device)
         self.L.ref_r3_mark_visible(means.shape[0], _p(means), _p(view), _p(proj), _p(present))
         return present
+
+
+def ref_ssim_module():
+    """The unmodified reference fused-ssim extension (oracle/_ref/fused_ssim_cuda_ref.so), or None."""
+    path = os.path.join(REF_DIR, "fused_ssim_cuda_ref.so")
+    if not os.path.exists(path):
+        return None
+    if "fused_ssim_cuda_ref" not in _libs:
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("fused_ssim_cuda_ref", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        _libs["fused_ssim_cuda_ref"] = mod
+    return _libs["fused_ssim_cuda_ref"]

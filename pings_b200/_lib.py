@@ -136,6 +136,10 @@ def lib() -> C.CDLL:
     L.pg_sdf_query.restype = C.c_int
     L.pg_sdf_query.argtypes = [C.POINTER(PgNeuralMap), C.POINTER(PgQueryArgs), C.POINTER(PgMlp), C.c_float, C.c_int64,
                                fp, fp, fp, fp, fp]
+    L.pg_ssim_forward.restype = C.c_int
+    L.pg_ssim_forward.argtypes = [C.c_int] * 4 + [C.c_float] * 2 + [fp] * 7
+    L.pg_ssim_backward.restype = C.c_int
+    L.pg_ssim_backward.argtypes = [C.c_int] * 4 + [C.c_float] * 2 + [fp, fp, fp, C.c_float, fp, fp, fp, fp, fp]
     _declare_optional(L)
     _lib = L
     return L
