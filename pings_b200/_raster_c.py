@@ -173,6 +173,109 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             tau_full if full_tau else dL_dtau)
 
 
+def rasterize_gaussians_surfel(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                               cov3D_precomp, viewmatrix, projmatrix, projmatrix_raw, prcppoint, patchbbox, tan_fovx,
+                               tan_fovy, image_height, image_width, sh, degree, campos, prefiltered, debug, config):
+    """RS/rasterize_points.cu:35-131 (same positional arguments, same 10-tuple)."""
+    lib = L.lib()
+    if means3D.ndim != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    dev = means3D.device
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    fopt = dict(dtype=torch.float32, device=dev)
+    out_color = torch.zeros(3, H, W, **fopt)
+    out_normal = torch.zeros(3, H, W, **fopt)
+    out_depth = torch.zeros(1, H, W, **fopt)
+    out_opac = torch.zeros(1, H, W, **fopt)
+    radii = torch.zeros(P, dtype=torch.int32, device=dev)
+    contributions = torch.zeros(P, **fopt)
+    bopt = dict(dtype=torch.uint8, device=dev)
+    geom = torch.empty(0, **bopt)
+    binning = torch.empty(0, **bopt)
+    img = torch.empty(0, **bopt)
+    rendered = 0
+    if P != 0:
+        V = L.PG_VARIANT_SURFEL
+        M = sh.size(1) if sh.numel() != 0 else 0
+        background, means3D, colors, opacity = _f32c(background), _f32c(means3D), _f32c(colors), _f32c(opacity)
+        scales, rotations, cov3D_precomp, sh = _f32c(scales), _f32c(rotations), _f32c(cov3D_precomp), _f32c(sh)
+        viewmatrix, projmatrix, campos = _f32c(viewmatrix), _f32c(projmatrix), _f32c(campos)
+        prcppoint, patchbbox, config = (_f32c(t.to(dev)) for t in (prcppoint, patchbbox, config))
+        prm = _params(V, P, W, H, tan_fovx, tan_fovy, scale_modifier, prefiltered, debug, degree, M, background,
+                      viewmatrix, projmatrix, projmatrix_raw, campos, patchbbox, prcppoint, config)
+        g = _gauss(means3D, sh, colors, opacity, scales, rotations, cov3D_precomp)
+        with torch.cuda.device(dev):
+            st = _stream(dev)
+            geom = torch.empty(lib.pg_raster_geom_bytes(V, P), **bopt)
+            img = torch.empty(lib.pg_raster_image_bytes(V, W, H), **bopt)
+            n = C.c_int64(0)
+            L.check(lib.pg_raster_forward_stage1(C.byref(prm), C.byref(g), geom.data_ptr(), geom.numel(),
+                                                 radii.data_ptr(), C.byref(n), st), "surfel forward (stage 1)")
+            rendered = int(n.value)
+            binning = torch.empty(lib.pg_raster_binning_bytes(V, W, H, rendered), **bopt)
+            out = L.PgRasterFwdOut()
+            out.out_color, out.out_depth, out.out_opacity = out_color.data_ptr(), out_depth.data_ptr(), out_opac.data_ptr()
+            out.radii, out.out_normal, out.contributions = radii.data_ptr(), out_normal.data_ptr(), contributions.data_ptr()
+            L.check(lib.pg_raster_forward_stage2(C.byref(prm), C.byref(g), geom.data_ptr(), binning.data_ptr(),
+                                                 binning.numel(), img.data_ptr(), rendered, C.byref(out), st),
+                    "surfel forward (stage 2)")
+    return rendered, out_color, out_normal, out_depth, out_opac, radii, contributions, geom, binning, img
+
+
+def rasterize_gaussians_surfel_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                        cov3D_precomp, viewmatrix, projmatrix, projmatrix_raw, prcppoint, patchbbox,
+                                        tan_fovx, tan_fovy, dL_dout_color, dL_dout_normal, dL_dout_depth, dL_dout_opac,
+                                        sh, degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, config,
+                                        full_tau=False):
+    """RS/rasterize_points.cu:133-233.  Same 9-tuple; the pose gradient is already reduced to [1,6]
+    unless full_tau=True (see rasterize_gaussians_backward)."""
+    lib = L.lib()
+    dev = means3D.device
+    P = means3D.size(0)
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    M = sh.size(1) if sh.numel() != 0 else 0
+    fopt = dict(dtype=torch.float32, device=dev)
+    dL_dmeans3D = torch.empty(P, 3, **fopt)
+    dL_dmeans2D = torch.empty(P, 3, **fopt)
+    dL_dcolors = torch.empty(P, 3, **fopt)
+    dL_dopacity = torch.empty(P, 1, **fopt)
+    dL_dcov3D = torch.empty(P, 6, **fopt)
+    dL_dsh = torch.empty(P, M, 3, **fopt)
+    dL_dscales = torch.empty(P, 3, **fopt)
+    dL_drotations = torch.empty(P, 4, **fopt)
+    dL_dtau = torch.zeros(1, 6, **fopt)
+    tau_full = torch.empty(P, 6, **fopt) if full_tau else None
+    if P != 0:
+        V = L.PG_VARIANT_SURFEL
+        background, means3D, colors = _f32c(background), _f32c(means3D), _f32c(colors)
+        scales, rotations, cov3D_precomp, sh = _f32c(scales), _f32c(rotations), _f32c(cov3D_precomp), _f32c(sh)
+        viewmatrix, projmatrix, projmatrix_raw, campos = _f32c(viewmatrix), _f32c(projmatrix), _f32c(projmatrix_raw), _f32c(campos)
+        prcppoint, patchbbox, config = (_f32c(t.to(dev)) for t in (prcppoint, patchbbox, config))
+        dL_dout_color, dL_dout_normal = _f32c(dL_dout_color), _f32c(dL_dout_normal)
+        dL_dout_depth, dL_dout_opac = _f32c(dL_dout_depth), _f32c(dL_dout_opac)
+        prm = _params(V, P, W, H, tan_fovx, tan_fovy, scale_modifier, False, debug, degree, M, background, viewmatrix,
+                      projmatrix, projmatrix_raw, campos, patchbbox, prcppoint, config)
+        g = _gauss(means3D, sh, colors, None, scales, rotations, cov3D_precomp)
+        bi = L.PgRasterBwdIn()
+        bi.dL_dout_color, bi.dL_dout_depth, bi.radii = dL_dout_color.data_ptr(), dL_dout_depth.data_ptr(), radii.data_ptr()
+        bi.dL_dout_normal, bi.dL_dout_opac = dL_dout_normal.data_ptr(), dL_dout_opac.data_ptr()
+        bo = L.PgRasterBwdOut()
+        bo.dL_dmeans2D, bo.dL_dcolors, bo.dL_dopacity = dL_dmeans2D.data_ptr(), dL_dcolors.data_ptr(), dL_dopacity.data_ptr()
+        bo.dL_dmeans3D, bo.dL_dcov3D, bo.dL_dsh = dL_dmeans3D.data_ptr(), dL_dcov3D.data_ptr(), L.ptr(dL_dsh)
+        bo.dL_dscales, bo.dL_drotations = dL_dscales.data_ptr(), dL_drotations.data_ptr()
+        bo.dL_dtau = dL_dtau.data_ptr()
+        bo.dL_dtau_full = L.ptr(tau_full)
+        with torch.cuda.device(dev):
+            L.check(lib.pg_raster_backward(C.byref(prm), C.byref(g), geomBuffer.data_ptr(), L.ptr(binningBuffer),
+                                           imageBuffer.data_ptr(), int(R), C.byref(bi), C.byref(bo), _stream(dev)),
+                    "surfel backward")
+        if not scales.numel():
+            dL_dscales.zero_()
+            dL_drotations.zero_()
+    return (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations,
+            tau_full if full_tau else dL_dtau)
+
+
 def debug_views(variant, P, W, H, R, geom, binning, img):
     """Typed torch views of the opaque workspaces, for the parity tests."""
     lib = L.lib()

@@ -1,5 +1,5 @@
 // C-ABI entry points of the rasterizer (see include/pings_b200.h).
-#include "pg_raster3_bwd.cuh"
+#include "pg_rasters_bwd.cuh"
 
 namespace pg {
 struct HostSlot {
@@ -29,6 +29,7 @@ static bool params_ok(const PgRasterParams* p) {
   if (p->variant != PG_VARIANT_3DGS && p->variant != PG_VARIANT_SURFEL) return false;
   if (p->P < 0 || p->image_width <= 0 || p->image_height <= 0) return false;
   if (!p->viewmatrix || !p->projmatrix || !p->bg) return false;
+  if (p->variant == PG_VARIANT_SURFEL && (!p->patch_bbox || !p->config)) return false;
   return true;
 }
 }  // namespace pg
@@ -48,12 +49,15 @@ size_t pg_raster_binning_bytes(int variant, int width, int height, int64_t num_r
 
 int pg_mark_visible(int variant, int P, const float* means3D, const float* viewmatrix,
                     const float* projmatrix, uint8_t* present, void* stream) {
-  (void)projmatrix;
   if (P < 0 || (P > 0 && (!means3D || !viewmatrix || !present))) return PG_ERR_ARG;
-  if (variant != PG_VARIANT_3DGS) return PG_ERR_UNSUPPORTED;
+  if (variant != PG_VARIANT_3DGS && variant != PG_VARIANT_SURFEL) return PG_ERR_ARG;
+  if (variant == PG_VARIANT_SURFEL && P > 0 && !projmatrix) return PG_ERR_ARG;
   if (P == 0) return PG_OK;
   cudaStream_t st = (cudaStream_t)stream;
-  r3_mark_visible_kernel<<<div_up(P, 256), 256, 0, st>>>(P, means3D, viewmatrix, present);
+  if (variant == PG_VARIANT_SURFEL)
+    rs_mark_visible_kernel<<<div_up(P, 256), 256, 0, st>>>(P, means3D, viewmatrix, projmatrix, present);
+  else
+    r3_mark_visible_kernel<<<div_up(P, 256), 256, 0, st>>>(P, means3D, viewmatrix, present);
   PG_LAUNCH_CHECK(0, st);
   return PG_OK;
 }
@@ -68,7 +72,8 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
   if (!g->colors_precomp && !g->shs) return PG_ERR_ARG;
   if (!g->cov3D_precomp && (!g->scales || !g->rotations)) return PG_ERR_ARG;
   if (!g->colors_precomp && !prm->campos) return PG_ERR_ARG;
-  if (prm->variant != PG_VARIANT_3DGS) return PG_ERR_UNSUPPORTED;
+  const bool surfel = prm->variant == PG_VARIANT_SURFEL;
+  if (surfel && !g->rotations) return PG_ERR_ARG;  // RS forward.cu:263 reads rotations unconditionally
   const int W = prm->image_width, H = prm->image_height;
   const int gx = div_up(W, kTile), gy = div_up(H, kTile);
   if ((int64_t)gx * gy > 65535) return PG_ERR_UNSUPPORTED;
@@ -90,8 +95,19 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
   a.prefiltered = prm->prefiltered;
   {
     Phase ph("preprocess_fwd", st);
-    r3_preprocess_kernel<<<div_up(P, 256), 256, 0, st>>>(a, radii, ws.rec, ws.dkey, ws.tiles, ws.rect, ws.clamped,
-                                                        ws.total);
+    if (surfel) {
+      RSPreArgs b;
+      b.P = P; b.D = a.D; b.M = a.M; b.W = W; b.H = H; b.gx = gx; b.gy = gy;
+      b.means = a.means; b.scales = a.scales; b.rots = a.rots; b.opac = a.opac; b.shs = a.shs;
+      b.cov3D_pre = a.cov3D_pre; b.colors_pre = a.colors_pre; b.view = a.view; b.proj = a.proj; b.campos = a.campos;
+      b.patch_bbox = prm->patch_bbox; b.config = prm->config;
+      b.mod = a.mod; b.tanx = a.tanx; b.tany = a.tany; b.fx = a.fx; b.fy = a.fy; b.prefiltered = a.prefiltered;
+      rs_preprocess_kernel<<<div_up(P, 256), 256, 0, st>>>(b, radii, ws.rec, ws.ext, ws.zyv, ws.dkey, ws.tiles,
+                                                          ws.rect, ws.clamped, ws.total);
+    } else {
+      r3_preprocess_kernel<<<div_up(P, 256), 256, 0, st>>>(a, radii, ws.rec, ws.dkey, ws.tiles, ws.rect, ws.clamped,
+                                                          ws.total);
+    }
   }
   PG_LAUNCH_CHECK(prm->debug, st);
   PG_CUDA(cudaMemcpyAsync(g_slot.pinned, ws.total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
@@ -113,12 +129,13 @@ int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, vo
                              size_t binning_bytes, void* image_ws, int64_t num_rendered,
                              const PgRasterFwdOut* out, void* stream) {
   if (!params_ok(prm) || !g || !out || num_rendered < 0) return PG_ERR_ARG;
-  if (prm->variant != PG_VARIANT_3DGS) return PG_ERR_UNSUPPORTED;
+  const bool surfel = prm->variant == PG_VARIANT_SURFEL;
   if (!image_ws || !out->out_color || !out->out_depth || !out->out_opacity) return PG_ERR_ARG;
+  if (surfel && !out->out_normal) return PG_ERR_ARG;
   const int P = prm->P, W = prm->image_width, H = prm->image_height;
   const int gx = div_up(W, kTile), gy = div_up(H, kTile);
   if ((int64_t)gx * gy > 65535) return PG_ERR_UNSUPPORTED;
-  if (P > 0 && (!geom_ws || !out->n_touched)) return PG_ERR_ARG;
+  if (P > 0 && (!geom_ws || (surfel ? !out->contributions : !out->n_touched))) return PG_ERR_ARG;
   if (num_rendered > 0 && (!binning_ws || binning_bytes < carve_binning(num_rendered, nullptr, nullptr)))
     return PG_ERR_WORKSPACE;
   cudaStream_t st = (cudaStream_t)stream;
@@ -136,9 +153,15 @@ int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, vo
   PG_LAUNCH_CHECK(prm->debug, st);
   {
     Phase ph("render_fwd", st);
-    r3_render_fwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
-                                                        out->out_color, out->out_depth, out->out_opacity, iw.final_T,
-                                                        iw.n_contrib, out->n_touched);
+    if (surfel)
+      rs_render_fwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, gw.ext, gw.zyv,
+                                                          prm->bg, prm->config, out->out_color, out->out_normal,
+                                                          out->out_depth, out->out_opacity, iw.final_T, iw.final_D,
+                                                          iw.n_contrib, out->contributions);
+    else
+      r3_render_fwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
+                                                          out->out_color, out->out_depth, out->out_opacity,
+                                                          iw.final_T, iw.n_contrib, out->n_touched);
   }
   PG_LAUNCH_CHECK(prm->debug, st);
   return PG_OK;
@@ -148,7 +171,8 @@ int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g, void* ge
                        void* image_ws, int64_t num_rendered, const PgRasterBwdIn* in, const PgRasterBwdOut* out,
                        void* stream) {
   if (!params_ok(prm) || !g || !in || !out || num_rendered < 0) return PG_ERR_ARG;
-  if (prm->variant != PG_VARIANT_3DGS) return PG_ERR_UNSUPPORTED;
+  const bool surfel = prm->variant == PG_VARIANT_SURFEL;
+  if (surfel && (!in->dL_dout_normal || !in->dL_dout_opac)) return PG_ERR_ARG;
   const int P = prm->P, W = prm->image_width, H = prm->image_height;
   if (P == 0) {
     if (out->dL_dtau) PG_CUDA(cudaMemsetAsync(out->dL_dtau, 0, 6 * sizeof(float), (cudaStream_t)stream));
@@ -168,14 +192,20 @@ int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g, void* ge
   carve_geom(prm->variant, P, geom_ws, &gw);
   carve_binning(num_rendered, binning_ws, &bw);
   carve_image(prm->variant, W, H, image_ws, &iw);
-  PG_CUDA(cudaMemsetAsync(gw.gacc, 0, sizeof(float4) * 3 * (size_t)P, st));
+  PG_CUDA(cudaMemsetAsync(gw.gacc, 0, sizeof(float4) * gw.gacc_count, st));
   PG_CUDA(cudaMemsetAsync(gw.tau_acc, 0, sizeof(double) * 8, st));
   if (num_rendered > 0) {
     const uint32_t* point_list = sorted_point_list(bw, W, H);
     Phase ph("render_bwd", st);
-    r3_render_bwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
-                                                        iw.final_T, iw.n_contrib, in->dL_dout_color,
-                                                        in->dL_dout_depth, gw.gacc);
+    if (surfel)
+      rs_render_bwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, gw.ext, gw.zyv,
+                                                          prm->bg, prm->config, iw.final_T, iw.final_D, iw.n_contrib,
+                                                          in->dL_dout_color, in->dL_dout_normal, in->dL_dout_depth,
+                                                          in->dL_dout_opac, gw.gacc);
+    else
+      r3_render_bwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
+                                                          iw.final_T, iw.n_contrib, in->dL_dout_color,
+                                                          in->dL_dout_depth, gw.gacc);
     PG_LAUNCH_CHECK(prm->debug, st);
   }
   R3BwdPreArgs a;
@@ -190,9 +220,11 @@ int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g, void* ge
   a.dL_dmeans3D = out->dL_dmeans3D; a.dL_dcov3D = out->dL_dcov3D; a.dL_dsh = g->shs ? out->dL_dsh : nullptr;
   a.dL_dscales = out->dL_dscales; a.dL_drots = out->dL_drotations;
   a.dL_dtau_full = out->dL_dtau_full; a.tau_acc = gw.tau_acc; a.dL_dtau = out->dL_dtau;
+  a.ext = gw.ext; a.zyv = gw.zyv; a.config = prm->config;
   {
     Phase ph("preprocess_bwd", st);
-    r3_preprocess_bwd_kernel<<<div_up(P, 256), 256, 0, st>>>(a);
+    if (surfel) r3_preprocess_bwd_kernel<true><<<div_up(P, 256), 256, 0, st>>>(a);
+    else r3_preprocess_bwd_kernel<false><<<div_up(P, 256), 256, 0, st>>>(a);
   }
   PG_LAUNCH_CHECK(prm->debug, st);
   return PG_OK;

@@ -240,6 +240,26 @@ __global__ void __launch_bounds__(kRThreads) r3_render_bwd_kernel(
 }
 
 // ---- fused per-Gaussian backward ----------------------------------------------------------
+// Surfel covariance with the `(mod*surface) ? 0 : scale.z` rule (RS forward.cu:162-202), from a quaternion.
+__device__ __forceinline__ void cov3d_surfel_q(float sx, float sy, float sz, float mod, bool surface, float4 q,
+                                               float* cov6) {
+  const float zs = (mod * (surface ? 1.f : 0.f)) != 0.f ? 0.f : sz;
+  // (mod*zs) would rescale: build S explicitly instead of reusing cov3d_from_scale_rot's mod*sz
+  M3 S = {{{0, 0, 0}, {0, 0, 0}, {0, 0, 0}}};
+  S.c[0][0] = mod * sx;
+  S.c[1][1] = mod * sy;
+  S.c[2][2] = zs;
+  const float r = q.x, x = q.y, y = q.z, z = q.w;
+  M3 R;
+  R.c[0][0] = 1.f - 2.f * (y * y + z * z); R.c[0][1] = 2.f * (x * y - r * z); R.c[0][2] = 2.f * (x * z + r * y);
+  R.c[1][0] = 2.f * (x * y + r * z); R.c[1][1] = 1.f - 2.f * (x * x + z * z); R.c[1][2] = 2.f * (y * z - r * x);
+  R.c[2][0] = 2.f * (x * z - r * y); R.c[2][1] = 2.f * (y * z + r * x); R.c[2][2] = 1.f - 2.f * (x * x + y * y);
+  M3 Mm = m3_mul(S, R);
+  M3 Sg = m3_mul(m3_transpose(Mm), Mm);
+  cov6[0] = Sg.c[0][0]; cov6[1] = Sg.c[0][1]; cov6[2] = Sg.c[0][2];
+  cov6[3] = Sg.c[1][1]; cov6[4] = Sg.c[1][2]; cov6[5] = Sg.c[2][2];
+}
+
 struct R3BwdPreArgs {
   int P, D, M, W, H;
   const float *means, *scales, *rots, *shs, *cov3D_pre, *view, *proj, *proj_raw, *campos;
@@ -251,12 +271,20 @@ struct R3BwdPreArgs {
   float* dL_dtau_full;  // [P,6] or null
   double* tau_acc;      // [6] + counter at [7] (as unsigned long long)
   float* dL_dtau;       // [6]
+  // surfel variant only (pg_rasters_fwd.cuh): normal/zx record, zy, config flags
+  const float4* ext;
+  const float* zyv;
+  const float* config;
 };
 
 __device__ __forceinline__ float3 cross3(const float3& a, const float3& b) {
   return make_float3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
 }
 
+// SURFEL = true adds the differences of RS cuda_rasterizer/backward.cu:362-452,457-582: 4-float4
+// gradient records, the z-scale rule in the recomputed covariance, the per-pixel-depth term of
+// dL_dmean2D, dL_dnormal -> last row of dL_dRt, dL_dscale.z = 0 when `surface`.
+template <bool SURFEL>
 __global__ void __launch_bounds__(256) r3_preprocess_bwd_kernel(R3BwdPreArgs a) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   float tau[6] = {0, 0, 0, 0, 0, 0};
@@ -265,10 +293,21 @@ __global__ void __launch_bounds__(256) r3_preprocess_bwd_kernel(R3BwdPreArgs a) 
     float dmean2[2] = {0, 0}, dcol[3] = {0, 0, 0}, dopac = 0.f;
     const bool vis = a.radii[idx] > 0;
     if (vis) {
-      const float4 g0 = a.gacc[3 * (size_t)idx + 0];
-      const float4 g1 = a.gacc[3 * (size_t)idx + 1];
-      const float4 g2 = a.gacc[3 * (size_t)idx + 2];
+      constexpr int kStride = SURFEL ? 4 : 3;
+      const float4 g0 = a.gacc[kStride * (size_t)idx + 0];
+      const float4 g1 = a.gacc[kStride * (size_t)idx + 1];
+      const float4 g2 = a.gacc[kStride * (size_t)idx + 2];
       dmean2[0] = g0.x; dmean2[1] = g0.y;
+      bool surface = false;
+      float3 dL_dcamN = make_float3(0.f, 0.f, 0.f);
+      if (SURFEL) {
+        surface = a.config[0] > 0;
+        // per-pixel-depth term (RS backward.cu:894-897): -sum(dL_dpixD) * (zx, zy)
+        dmean2[0] += -g1.w * a.ext[idx].w;
+        dmean2[1] += -g1.w * a.zyv[idx];
+        const float4 g3 = a.gacc[kStride * (size_t)idx + 3];
+        dL_dcamN = make_float3(g3.x, g3.y, g3.z);
+      }
       const float3 dL_dconic = make_float3(g0.z, g0.w, g1.x);
       dopac = g1.y;
       const float dL_ddepth = g1.z;
@@ -284,7 +323,8 @@ __global__ void __launch_bounds__(256) r3_preprocess_bwd_kernel(R3BwdPreArgs a) 
       } else {
         q = reinterpret_cast<const float4*>(a.rots)[idx];
         sc = make_float3(a.scales[3 * idx], a.scales[3 * idx + 1], a.scales[3 * idx + 2]);
-        cov3d_from_scale_rot(sc.x, sc.y, sc.z, a.mod, q, cov6);
+        if (SURFEL) cov3d_surfel_q(sc.x, sc.y, sc.z, a.mod, surface, q, cov6);
+        else cov3d_from_scale_rot(sc.x, sc.y, sc.z, a.mod, q, cov6);
       }
       // ---- conic -> cov2D -> cov3D, T, J, t (computeCov2DCUDA) ----
       Cov2DAux ax;
@@ -422,11 +462,18 @@ __global__ void __launch_bounds__(256) r3_preprocess_bwd_kernel(R3BwdPreArgs a) 
         dscale[0] = Rt.c[0][0] * dMt.c[0][0] + Rt.c[0][1] * dMt.c[0][1] + Rt.c[0][2] * dMt.c[0][2];
         dscale[1] = Rt.c[1][0] * dMt.c[1][0] + Rt.c[1][1] * dMt.c[1][1] + Rt.c[1][2] * dMt.c[1][2];
         dscale[2] = Rt.c[2][0] * dMt.c[2][0] + Rt.c[2][1] * dMt.c[2][1] + Rt.c[2][2] * dMt.c[2][2];
+        if (SURFEL && surface) dscale[2] = 0.f;
 #pragma unroll
         for (int i = 0; i < 3; ++i) {
           dMt.c[0][i] *= s0;
           dMt.c[1][i] *= s1;
           dMt.c[2][i] *= s2;
+        }
+        if (SURFEL) {  // loss gradient of the normal output w.r.t. R (RS backward.cu:427-436)
+          const float3 dwn = xform_vec_4x3_T(dL_dcamN, a.view);
+          dMt.c[2][0] += dwn.x;
+          dMt.c[2][1] += dwn.y;
+          dMt.c[2][2] += dwn.z;
         }
         drot[0] = 2 * z * (dMt.c[0][1] - dMt.c[1][0]) + 2 * y * (dMt.c[2][0] - dMt.c[0][2]) + 2 * x * (dMt.c[1][2] - dMt.c[2][1]);
         drot[1] = 2 * y * (dMt.c[1][0] + dMt.c[0][1]) + 2 * z * (dMt.c[2][0] + dMt.c[0][2]) + 2 * r * (dMt.c[1][2] - dMt.c[2][1]) - 4 * x * (dMt.c[2][2] + dMt.c[1][1]);

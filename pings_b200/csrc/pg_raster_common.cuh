@@ -19,7 +19,8 @@ constexpr int kTile = 16;
 
 struct GeomWs {
   float4* rec;            // [3P] packed per-Gaussian record (see pg_raster3.cu)
-  float4* rec_ext;        // [3P] surfel extras (normal, Jinv...) or null
+  float4* ext;            // [P] surfel: (n_view.xyz, zx) or null (pg_rasters_fwd.cuh)
+  float* zyv;             // [P] surfel: zy or null
   uint32_t* dkey;         // [P] depth bits, 0xFFFFFFFF when culled
   uint32_t* tiles;        // [P] tiles touched
   uint2* rect;            // [P] x0 | x1<<16 , y0 | y1<<16
@@ -32,8 +33,8 @@ struct GeomWs {
   uint32_t* sort_scratch; // radix/scan scratch for P items
   unsigned long long* total;  // [1] number of instances
   double* tau_acc;        // [8] pose-gradient accumulators (6 used) + block counter
-  float4* gacc;           // [3P] backward per-Gaussian gradient accumulation records
-  float4* gacc_ext;       // [P]  surfel: dL_dnormal accumulation
+  float4* gacc;           // [3P] (3DGS) / [4P] (surfel) backward gradient accumulation records
+  size_t gacc_count;      // number of float4 in gacc
 };
 
 inline size_t carve_geom(int variant, int P, void* base, GeomWs* ws) {
@@ -41,7 +42,8 @@ inline size_t carve_geom(int variant, int P, void* base, GeomWs* ws) {
   GeomWs w;
   size_t p = (size_t)(P > 0 ? P : 1);
   w.rec = c.take<float4>(3 * p);
-  w.rec_ext = variant == PG_VARIANT_SURFEL ? c.take<float4>(4 * p) : nullptr;
+  w.ext = variant == PG_VARIANT_SURFEL ? c.take<float4>(p) : nullptr;
+  w.zyv = variant == PG_VARIANT_SURFEL ? c.take<float>(p) : nullptr;
   w.dkey = c.take<uint32_t>(p);
   w.tiles = c.take<uint32_t>(p);
   w.rect = c.take<uint2>(p);
@@ -54,8 +56,8 @@ inline size_t carve_geom(int variant, int P, void* base, GeomWs* ws) {
   w.sort_scratch = c.take<uint32_t>(sort_scratch_elems(p));
   w.total = c.take<unsigned long long>(2);
   w.tau_acc = c.take<double>(8);
-  w.gacc = c.take<float4>(3 * p);
-  w.gacc_ext = variant == PG_VARIANT_SURFEL ? c.take<float4>(p) : nullptr;
+  w.gacc_count = (variant == PG_VARIANT_SURFEL ? 4 : 3) * p;
+  w.gacc = c.take<float4>(w.gacc_count);
   if (ws) *ws = w;
   return c.total();
 }

@@ -1,0 +1,253 @@
+// Gaussian-surfel backward kernels: per-tile blend backward (colour, normal, depth, opacity
+// cotangents) with warp-shuffle gradient reduction.  The per-surfel backward (conic -> cov3D ->
+// scale/rot, mean2D -> mean3D, normal -> rotation, pose gradient) is the templated kernel in
+// pg_raster3_bwd.cuh.
+//
+// Reference behaviour: RS cuda_rasterizer/backward.cu:585-914 (renderCUDA; per-thread atomics
+// there), :160-358 (computeCov2DCUDA), :362-452 (computeCov3D), :457-582 (preprocessCUDA).
+#pragma once
+#include "pg_raster3_bwd.cuh"
+#include "pg_rasters_fwd.cuh"
+
+namespace pg {
+
+// Sum 16 per-lane values over the 32 lanes of a warp with a halving butterfly (8+4+2+1+1 = 16
+// shuffles); total k ends up in lane 2*bitrev-ish index below and is stored to dst[k].
+__device__ __forceinline__ void warp_reduce16_store(float (&v)[16], int lane, float* dst) {
+  const unsigned full = 0xffffffffu;
+  const bool u4 = lane & 16;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const float send = u4 ? v[k] : v[k + 8];
+    const float keep = u4 ? v[k + 8] : v[k];
+    v[k] = keep + __shfl_xor_sync(full, send, 16);
+  }
+  const bool u3 = lane & 8;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float send = u3 ? v[k] : v[k + 4];
+    const float keep = u3 ? v[k + 4] : v[k];
+    v[k] = keep + __shfl_xor_sync(full, send, 8);
+  }
+  const bool u2 = lane & 4;
+#pragma unroll
+  for (int k = 0; k < 2; ++k) {
+    const float send = u2 ? v[k] : v[k + 2];
+    const float keep = u2 ? v[k + 2] : v[k];
+    v[k] = keep + __shfl_xor_sync(full, send, 4);
+  }
+  const bool u1 = lane & 2;
+  {
+    const float send = u1 ? v[0] : v[1];
+    const float keep = u1 ? v[1] : v[0];
+    v[0] = keep + __shfl_xor_sync(full, send, 2);
+  }
+  v[0] += __shfl_xor_sync(full, v[0], 1);
+  const int index = (u4 ? 8 : 0) + (u3 ? 4 : 0) + (u2 ? 2 : 0) + (u1 ? 1 : 0);
+  if (!(lane & 1)) dst[index] = v[0];
+}
+
+struct RSBwdSlab {
+  RSSlab in;
+  float acc[2][kRBatch][16];  // per-warp partial sums of the current batch
+  uint32_t flag[2][kRBatch];
+  uint32_t wmax[2];
+};
+
+// Gradient accumulation record per surfel (4 x float4):
+//   gacc[4i+0] = (dL_dmean2D.x, dL_dmean2D.y, dL_dconic.x, dL_dconic.y)
+//   gacc[4i+1] = (dL_dconic.w, dL_dopacity, dL_ddepth, S = sum of dL_dpixD over blended pairs)
+//   gacc[4i+2] = (dL_dcolor.r, .g, .b, 0)
+//   gacc[4i+3] = (dL_dnormal.x, .y, .z, 0)      (already x10, RS backward.cu:783)
+// The per-pixel-depth term of dL_dmean2D (RS backward.cu:894-897) is -S * (zx, zy): it does not
+// depend on the pixel, so it is applied once per surfel in the per-surfel kernel.
+__global__ void __launch_bounds__(kRThreads) rs_render_bwd_kernel(
+    const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int gx,
+    const float4* __restrict__ rec, const float4* __restrict__ ext, const float* __restrict__ zyv,
+    const float* __restrict__ bg, const float* __restrict__ config, const float* __restrict__ final_T,
+    const float* __restrict__ final_D, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
+    const float* __restrict__ dL_dpix_normal, const float* __restrict__ dL_dpix_depth,
+    const float* __restrict__ dL_dpix_opac, float4* __restrict__ gacc) {
+  __shared__ RSBwdSlab sm;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tile = blockIdx.x;
+  const int tx = tile % gx, ty = tile / gx;
+  const int rx0 = tx * kTile, ry0 = ty * kTile + warp * 8;
+  const int qx = rx0 + (lane & 7) * 2, qy = ry0 + (lane >> 3) * 2;
+  const float fxs[2] = {(float)qx, (float)(qx + 1)};
+  const float fys[2] = {(float)qy, (float)(qy + 1)};
+  const float wx0 = (float)rx0, wx1 = (float)min(rx0 + 15, W - 1);
+  const float wy0 = (float)ry0, wy1 = (float)min(ry0 + 7, H - 1);
+  const size_t HW = (size_t)H * W;
+  const bool surface = config[0] > 0, normalize_depth = config[1] > 0, ppd = surface && (config[2] > 0);
+
+  float T[4], Tfin[4], Dfin[4], acr[4][3], acn[4][3], acd[4], lalpha[4], lcol[4][3], lnrm[4][3], ldep[4];
+  float dpx[4][3], dpn[4][3], dpd[4], dpo[4], bgdot[4];
+  uint32_t lastc[4];
+  const float b0 = bg[0], b1 = bg[1], b2 = bg[2];
+  uint32_t my_max = 0;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int x = qx + (k & 1), y = qy + (k >> 1);
+    const bool in = x < W && y < H;
+    const size_t pix = (size_t)W * y + x;
+    Tfin[k] = in ? final_T[pix] : 0.f;
+    Dfin[k] = (in && normalize_depth) ? final_D[pix] : 0.f;
+    T[k] = Tfin[k];
+    lastc[k] = in ? n_contrib[pix] : 0u;
+    my_max = max(my_max, lastc[k]);
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+      dpx[k][ch] = in ? dL_dpix[ch * HW + pix] : 0.f;
+      dpn[k][ch] = in ? dL_dpix_normal[ch * HW + pix] : 0.f;
+      acr[k][ch] = acn[k][ch] = 0.f;
+      lcol[k][ch] = lnrm[k][ch] = 0.f;
+    }
+    dpd[k] = in ? dL_dpix_depth[pix] : 0.f;
+    dpo[k] = in ? dL_dpix_opac[pix] : 0.f;
+    acd[k] = 0.f; lalpha[k] = 0.f; ldep[k] = 0.f;
+    bgdot[k] = b0 * dpx[k][0] + b1 * dpx[k][1] + b2 * dpx[k][2];
+  }
+  const uint32_t wmax = __reduce_max_sync(0xffffffffu, my_max);
+  if (lane == 0) sm.wmax[warp] = wmax;
+  sm.flag[0][tid] = 0;
+  sm.flag[1][tid] = 0;
+  __syncthreads();
+  const uint2 range = ranges[tile];
+  const int n_eff = (int)min(max(sm.wmax[0], sm.wmax[1]), range.y - range.x);
+  const int rounds = (n_eff + kRBatch - 1) / kRBatch;
+  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+
+  if (tid < n_eff) rs_stage(sm.in, 0, tid, point_list[range.x + (n_eff - 1 - tid)], rec, ext, zyv);
+  cp_async_commit();
+  uint32_t nxt = 0;
+  if (kRBatch + tid < n_eff) nxt = point_list[range.x + (n_eff - 1 - kRBatch - tid)];
+
+  int cur = 0;
+  for (int r = 0; r < rounds; ++r) {
+    cp_async_wait_all();
+    __syncthreads();
+    if ((r + 1) * kRBatch + tid < n_eff) rs_stage(sm.in, cur ^ 1, tid, nxt, rec, ext, zyv);
+    cp_async_commit();
+    if ((r + 2) * kRBatch + tid < n_eff) nxt = point_list[range.x + (n_eff - 1 - (r + 2) * kRBatch - tid)];
+
+    const int cnt = min(kRBatch, n_eff - r * kRBatch);
+#pragma unroll 1
+    for (int g = 0; g < kRBatch / 32; ++g) {
+      const int j0 = g * 32 + lane;
+      bool hit = false;
+      if (j0 < cnt) {
+        const float4 e = sm.in.a[cur][j0];
+        const uint32_t pos0 = (uint32_t)(n_eff - 1 - (r * kRBatch + j0));
+        hit = (pos0 < wmax) && (e.x + e.z >= wx0) && (e.x - e.z <= wx1) && (e.y + e.w >= wy0) &&
+              (e.y - e.w <= wy1);
+      }
+      uint32_t m = __ballot_sync(0xffffffffu, hit);
+      while (m) {
+        const int j = g * 32 + (__ffs(m) - 1);
+        m &= m - 1;
+        const uint32_t pos = (uint32_t)(n_eff - 1 - (r * kRBatch + j));
+        const float4 e = sm.in.a[cur][j];
+        const float4 co = sm.in.b[cur][j];
+        float G[4], al[4], ddx[4], ddy[4];
+        bool act[4];
+        bool any = false;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          ddx[k] = e.x - fxs[k & 1];
+          ddy[k] = e.y - fys[k >> 1];
+          const float dist = (co.x * ddx[k] * ddx[k] + co.z * ddy[k] * ddy[k]) + 2 * co.y * ddx[k] * ddy[k];
+          const float power = -0.5f * dist;
+          G[k] = expf(power);
+          al[k] = fminf(0.99f, co.w * G[k]);
+          act[k] = (pos < lastc[k]) && !(power > 0.0f) && !(al[k] < 1.0f / 255.0f);
+          any |= act[k];
+        }
+        if (!__any_sync(0xffffffffu, any)) continue;
+        float v[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) v[q] = 0.f;
+        if (any) {
+          const float4 cd = sm.in.c[cur][j];
+          const float4 ne = sm.in.e[cur][j];
+          const float zyj = sm.in.zy[cur][j];
+          const float col[3] = {cd.y, cd.z, cd.w};
+          const float nrm[3] = {ne.x, ne.y, ne.z};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            if (act[k]) {
+              const float alpha = al[k];
+              T[k] = T[k] / (1.f - alpha);
+              const float dchannel_dcolor = alpha * T[k];
+              float dL_dalpha = 0.0f;
+#pragma unroll
+              for (int ch = 0; ch < 3; ++ch) {
+                acr[k][ch] = lalpha[k] * lcol[k][ch] + (1.f - lalpha[k]) * acr[k][ch];
+                lcol[k][ch] = col[ch];
+                dL_dalpha += (col[ch] - acr[k][ch]) * dpx[k][ch];
+                v[8 + ch] += dchannel_dcolor * dpx[k][ch];
+              }
+              if (surface) {
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) {
+                  acn[k][ch] = lalpha[k] * lnrm[k][ch] + (1.f - lalpha[k]) * acn[k][ch];
+                  lnrm[k][ch] = nrm[ch];
+                  dL_dalpha += (nrm[ch] - acn[k][ch]) * dpn[k][ch];
+                  v[11 + ch] += dchannel_dcolor * dpn[k][ch] * 10;
+                }
+              }
+              {
+                const float d_cur = cd.x - (ddx[k] * ne.w + ddy[k] * zyj);
+                acd[k] = lalpha[k] * ldep[k] + (1.f - lalpha[k]) * acd[k];
+                ldep[k] = d_cur;
+                float dL_dchannel = dpd[k], dL_dalpha_depth = 0.f;
+                if (normalize_depth) {
+                  dL_dchannel /= (1.f - Tfin[k]);
+                  dL_dalpha_depth += dpd[k] * Dfin[k] / (1.f - Tfin[k]) / (1.f - Tfin[k]) * -Tfin[k] / (1 - alpha) / T[k];
+                }
+                dL_dalpha_depth += (d_cur - acd[k]) * dL_dchannel;
+                v[6] += dchannel_dcolor * dL_dchannel * 1;
+                dL_dalpha += dL_dalpha_depth;
+              }
+              dL_dalpha *= T[k];
+              dL_dalpha += dpo[k] * Tfin[k] / (1 - alpha);
+              lalpha[k] = alpha;
+              dL_dalpha += (-Tfin[k] / (1.f - alpha)) * bgdot[k];
+              if (!normalize_depth) dL_dalpha += (-Tfin[k] / (1.f - alpha)) * (10 * dpd[k]);
+              const float dL_ddist = dL_dalpha * co.w * -0.5f * G[k];
+              v[0] += dL_ddist * 2 * (co.x * ddx[k] + co.y * ddy[k]) * ddelx_dx;
+              v[1] += dL_ddist * 2 * (co.z * ddy[k] + co.y * ddx[k]) * ddely_dy;
+              v[2] += dL_ddist * (ddx[k] * ddx[k]);
+              v[3] += dL_ddist * (1 * ddx[k] * ddy[k]);
+              v[4] += dL_ddist * (ddy[k] * ddy[k]);
+              v[5] += G[k] * dL_dalpha;
+              if (ppd) v[7] += dpd[k];
+            }
+          }
+        }
+        warp_reduce16_store(v, lane, &sm.acc[warp][j][0]);
+        if (lane == 0) sm.flag[warp][j] = 1;
+      }
+    }
+    __syncthreads();
+    {
+      const uint32_t f0 = sm.flag[0][tid], f1 = sm.flag[1][tid];
+      if (f0 | f1) {
+        float s[16];
+#pragma unroll
+        for (int q = 0; q < 16; ++q) s[q] = (f0 ? sm.acc[0][tid][q] : 0.f) + (f1 ? sm.acc[1][tid][q] : 0.f);
+        float4* dst = gacc + 4 * (size_t)sm.in.id[cur][tid];
+        atomicAdd(dst + 0, make_float4(s[0], s[1], s[2], s[3]));
+        atomicAdd(dst + 1, make_float4(s[4], s[5], s[6], s[7]));
+        atomicAdd(dst + 2, make_float4(s[8], s[9], s[10], 0.f));
+        if (surface) atomicAdd(dst + 3, make_float4(s[11], s[12], s[13], 0.f));
+        sm.flag[0][tid] = 0;
+        sm.flag[1][tid] = 0;
+      }
+    }
+    cur ^= 1;
+  }
+  cp_async_wait_all();
+}
+
+}  // namespace pg
