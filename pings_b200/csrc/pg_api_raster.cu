@@ -43,8 +43,8 @@ size_t pg_raster_image_bytes(int variant, int width, int height) {
   return carve_image(variant, width, height, nullptr, nullptr);
 }
 size_t pg_raster_binning_bytes(int variant, int width, int height, int64_t num_rendered) {
-  (void)variant; (void)width; (void)height;
-  return carve_binning(num_rendered, nullptr, nullptr);
+  (void)variant;
+  return carve_binning(num_rendered, width, height, nullptr, nullptr);
 }
 
 int pg_mark_visible(int variant, int P, const float* means3D, const float* viewmatrix,
@@ -103,10 +103,10 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
       b.patch_bbox = prm->patch_bbox; b.config = prm->config;
       b.mod = a.mod; b.tanx = a.tanx; b.tany = a.tany; b.fx = a.fx; b.fy = a.fy; b.prefiltered = a.prefiltered;
       rs_preprocess_kernel<<<div_up(P, 256), 256, 0, st>>>(b, radii, ws.rec, ws.ext, ws.zyv, ws.dkey, ws.tiles,
-                                                          ws.rect, ws.clamped, ws.total);
+                                                          ws.wts, ws.rect, ws.clamped, ws.total);
     } else {
-      r3_preprocess_kernel<<<div_up(P, 256), 256, 0, st>>>(a, radii, ws.rec, ws.dkey, ws.tiles, ws.rect, ws.clamped,
-                                                          ws.total);
+      r3_preprocess_kernel<<<div_up(P, 256), 256, 0, st>>>(a, radii, ws.rec, ws.dkey, ws.tiles, ws.wts, ws.rect,
+                                                          ws.clamped, ws.total);
     }
   }
   PG_LAUNCH_CHECK(prm->debug, st);
@@ -115,7 +115,7 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
   // depth ordering runs while the host waits for the count
   {
     Phase ph("depth_sort", st);
-    PG_CUDA(depth_order_and_offsets(ws, P, st));
+    PG_CUDA(depth_order_and_offsets(ws, P, bin_fast_path(gx * gy), st));
   }
   PG_LAUNCH_CHECK(prm->debug, st);
   PG_CUDA(cudaEventSynchronize(g_slot.ev));
@@ -136,14 +136,14 @@ int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, vo
   const int gx = div_up(W, kTile), gy = div_up(H, kTile);
   if ((int64_t)gx * gy > 65535) return PG_ERR_UNSUPPORTED;
   if (P > 0 && (!geom_ws || (surfel ? !out->contributions : !out->n_touched))) return PG_ERR_ARG;
-  if (num_rendered > 0 && (!binning_ws || binning_bytes < carve_binning(num_rendered, nullptr, nullptr)))
+  if (num_rendered > 0 && (!binning_ws || binning_bytes < carve_binning(num_rendered, W, H, nullptr, nullptr)))
     return PG_ERR_WORKSPACE;
   cudaStream_t st = (cudaStream_t)stream;
   GeomWs gw;
   BinWs bw;
   ImageWs iw;
   carve_geom(prm->variant, P, geom_ws, &gw);
-  carve_binning(num_rendered, binning_ws, &bw);
+  carve_binning(num_rendered, W, H, binning_ws, &bw);
   carve_image(prm->variant, W, H, image_ws, &iw);
   const uint32_t* point_list = nullptr;
   {
@@ -190,7 +190,7 @@ int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g, void* ge
   BinWs bw;
   ImageWs iw;
   carve_geom(prm->variant, P, geom_ws, &gw);
-  carve_binning(num_rendered, binning_ws, &bw);
+  carve_binning(num_rendered, W, H, binning_ws, &bw);
   carve_image(prm->variant, W, H, image_ws, &iw);
   PG_CUDA(cudaMemsetAsync(gw.gacc, 0, sizeof(float4) * gw.gacc_count, st));
   PG_CUDA(cudaMemsetAsync(gw.tau_acc, 0, sizeof(double) * 8, st));
@@ -238,7 +238,7 @@ int pg_raster_debug_views(int variant, int P, int width, int height, int64_t num
   BinWs bw;
   ImageWs iw;
   carve_geom(variant, P, geom_ws, &gw);
-  carve_binning(num_rendered, binning_ws, &bw);
+  carve_binning(num_rendered, width, height, binning_ws, &bw);
   carve_image(variant, width, height, image_ws, &iw);
   if (point_list) *point_list = sorted_point_list(bw, width, height);
   if (ranges) *ranges = reinterpret_cast<const uint32_t*>(iw.ranges);

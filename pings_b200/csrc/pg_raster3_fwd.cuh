@@ -99,8 +99,8 @@ struct R3PreArgs {
 
 __global__ void __launch_bounds__(256) r3_preprocess_kernel(R3PreArgs a, int* __restrict__ radii,
                                                             float4* __restrict__ rec, uint32_t* __restrict__ dkey,
-                                                            uint32_t* __restrict__ tiles, uint2* __restrict__ rect,
-                                                            uint8_t* __restrict__ clamped,
+                                                            uint32_t* __restrict__ tiles, uint32_t* __restrict__ wts,
+                                                            uint2* __restrict__ rect, uint8_t* __restrict__ clamped,
                                                             unsigned long long* __restrict__ total) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t my_tiles = 0;
@@ -160,7 +160,9 @@ __global__ void __launch_bounds__(256) r3_preprocess_kernel(R3PreArgs a, int* __
     } while (false);
     radii[idx] = radius;
     tiles[idx] = my_tiles;
+    wts[idx] = bin_weight(my_tiles);
     dkey[idx] = key;
+    if (!my_tiles) rect[idx] = make_uint2(0u, 0u);
   }
   // total instance count: warp reduce -> one atomic per warp
   uint32_t s = my_tiles;

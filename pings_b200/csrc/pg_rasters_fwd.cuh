@@ -129,8 +129,8 @@ __device__ __forceinline__ void rs_trap_if_prefiltered(int prefiltered) {
 __global__ void __launch_bounds__(256) rs_preprocess_kernel(RSPreArgs a, int* __restrict__ radii,
                                                             float4* __restrict__ rec, float4* __restrict__ ext,
                                                             float* __restrict__ zyv, uint32_t* __restrict__ dkey,
-                                                            uint32_t* __restrict__ tiles, uint2* __restrict__ rect,
-                                                            uint8_t* __restrict__ clamped,
+                                                            uint32_t* __restrict__ tiles, uint32_t* __restrict__ wts,
+                                                            uint2* __restrict__ rect, uint8_t* __restrict__ clamped,
                                                             unsigned long long* __restrict__ total) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t my_tiles = 0;
@@ -214,7 +214,9 @@ __global__ void __launch_bounds__(256) rs_preprocess_kernel(RSPreArgs a, int* __
     } while (false);
     radii[idx] = radius;
     tiles[idx] = my_tiles;
+    wts[idx] = bin_weight(my_tiles);
     dkey[idx] = key;
+    if (!my_tiles) rect[idx] = make_uint2(0u, 0u);
   }
   uint32_t s = my_tiles;
 #pragma unroll
