@@ -128,6 +128,24 @@ class NeuralPoints(nn.Module):
         return self.local_neural_points.shape[0]
 
     @classmethod
+    def from_reference(cls, ref) -> "NeuralPoints":
+        """Wrap a live reference `NeuralPoints` (model/neural_gaussians.py:20-120) without copying:
+        every tensor attribute (slot table, points, features, masks, local map) is shared, so the
+        reference's own `update` / `reset_local_map` keep maintaining the map while queries run here."""
+        self = cls.__new__(cls)
+        nn.Module.__init__(self)
+        for k, v in vars(ref).items():
+            if k.startswith("_"):
+                continue
+            setattr(self, k, v)
+        for k, v in ref._parameters.items():   # local_geo_features / local_color_features
+            setattr(self, k, v)
+        self.device = torch.device(ref.config.device)
+        if not hasattr(self, "neighbor_dx"):
+            self.set_search_neighborhood(ref.config.num_nei_cells, ref.config.search_alpha)
+        return self
+
+    @classmethod
     def from_state(cls, config, state: dict) -> "NeuralPoints":
         """Adopt tensors saved from a reference NeuralPoints (fixtures, pin_map.pth contents).
         `state["hash_slots"], state["hash_values"]` hold the occupied slot-table entries."""

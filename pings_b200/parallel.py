@@ -1,0 +1,118 @@
+"""Data-parallel plumbing for the hot path (one process per GPU, torch.distributed).
+
+The reference is single-GPU; this is the new design of DESIGN.md §6:
+views and SDF query rows are independent units and are sharded with no data-path collective;
+training adds exactly one exchange step per iteration, the sum of the parameter gradients
+(Gaussian parameters / neural-point features / decoder weights), done as ONE all-reduce over a
+flat fp32 buffer (NCCL over NVLink on the GPU box, gloo in the CPU tests).
+"""
+from __future__ import annotations
+
+from typing import Iterable, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def world() -> tuple[int, int]:
+    """(rank, world_size); (0, 1) when no process group is initialised."""
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_views(views: Sequence, rank: int, world_size: int) -> list:
+    """Round-robin view sharding: rank r renders views[r::world] (a batch of V views costs
+    ceil(V / world) renders per rank; cameras of a trajectory are interleaved so that the ranks'
+    workloads have the same depth complexity)."""
+    return list(views[rank::world_size])
+
+
+def shard_rows(n: int, rank: int, world_size: int) -> tuple[int, int]:
+    """Contiguous split of n query rows: [lo, hi) of this rank (sizes differ by at most 1)."""
+    base, rem = divmod(n, world_size)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+class FlatGradAllReduce:
+    """Sum (or average) the gradients of `params` over all ranks with a single collective.
+
+    Gradients are packed into one persistent flat buffer (so NCCL sees one large message: the
+    cost on NVSwitch is launch latency, not link count), all-reduced, and written back into
+    `p.grad`.  Parameters whose grad is None on this rank (e.g. neural points not visible in this
+    rank's views) contribute zeros.  With `side_stream=True` on CUDA the collective runs on its own
+    stream and `wait()` joins it, so that it overlaps independent backward work (the SDF branch).
+    """
+
+    def __init__(self, params: Iterable[torch.Tensor], average: bool = True, group=None, side_stream: bool = False):
+        self.params = [p for p in params]
+        if not self.params:
+            raise ValueError("FlatGradAllReduce: no parameters")
+        dev, dt = self.params[0].device, self.params[0].dtype
+        self.sizes = [p.numel() for p in self.params]
+        self.flat = torch.zeros(sum(self.sizes), dtype=dt, device=dev)
+        self.views = list(self.flat.split(self.sizes))
+        self.average = average
+        self.group = group
+        self.stream = torch.cuda.Stream(device=dev) if (side_stream and dev.type == "cuda") else None
+        self._work = None
+
+    @property
+    def nbytes(self) -> int:
+        return self.flat.numel() * self.flat.element_size()
+
+    def pack(self) -> None:
+        for p, v in zip(self.params, self.views):
+            if p.grad is None:
+                v.zero_()
+            else:
+                v.copy_(p.grad.reshape(-1))
+
+    def launch(self) -> None:
+        """pack + start the all-reduce (asynchronous when a side stream is used)."""
+        rank, ws = world()
+        self.pack()
+        if ws == 1:
+            return
+        if self.stream is not None:
+            self.stream.wait_stream(torch.cuda.current_stream(self.flat.device))
+            with torch.cuda.stream(self.stream):
+                dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+                if self.average:
+                    self.flat.div_(ws)
+        else:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+            if self.average:
+                self.flat.div_(ws)
+
+    def wait(self) -> None:
+        """Join the collective and scatter the reduced gradients back into p.grad."""
+        if self.stream is not None:
+            torch.cuda.current_stream(self.flat.device).wait_stream(self.stream)
+        for p, v in zip(self.params, self.views):
+            if p.grad is None:
+                p.grad = v.reshape(p.shape).clone()
+            else:
+                p.grad.copy_(v.reshape(p.shape))
+
+    def __call__(self) -> None:
+        self.launch()
+        self.wait()
+
+
+def replicas_in_sync(tensors: Iterable[torch.Tensor], group=None) -> bool:
+    """Debug check of DESIGN.md §6: replicated parameters must be bit-identical on every rank after a
+    step.  Compares an int64 checksum of the raw bits (all-gather of one scalar per rank)."""
+    rank, ws = world()
+    acc = None
+    for t in tensors:
+        bits = t.detach().contiguous().view(torch.uint8).to(torch.int64)
+        w = torch.arange(1, bits.numel() + 1, dtype=torch.int64, device=bits.device)
+        s = (bits.flatten() * (w % 65521)).sum()
+        acc = s if acc is None else acc * 31 + s
+    if ws == 1:
+        return True
+    gathered = [torch.zeros_like(acc) for _ in range(ws)]
+    dist.all_gather(gathered, acc, group=group)
+    return all(bool(g == gathered[0]) for g in gathered)
