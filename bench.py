@@ -145,10 +145,13 @@ def algorithmic_bytes(P: int, R: int, W: int, H: int) -> dict:
     """Per-launch algorithmic HBM bytes of each phase."""
     WH = W * H
     T = ((W + 15) // 16) * ((H + 15) // 16)
+    NC = min(4096, max(148, (4 << 20) // T))   # bin_max_chunks (pg_raster_common.cuh)
     return {
         "preprocess_fwd": 104 * P,                    # 44 B in + 60 B out per Gaussian
-        "depth_sort": (4 * (4 + 8 + 8) + 4) * P,      # 4 LSD passes over (u32 key, u32 value) + histogram read
-        "binning": 20 * P + 6 * R + 2 * (2 * R + 12 * R) + 2 * R + 8 * T,  # emit + 2 tile passes (hist+scatter) + ranges
+        "depth_sort": (4 * (4 + 8 + 8) + 4 + 16 + 12) * P,  # 4 LSD passes over (u32 key, u32 value) + rect gather + weight scan
+        # chunked counting sort (DESIGN.md 4.1): two walks over (id 4 B + rect 8 B) per Gaussian, one 4-B id
+        # write per instance, [tile][chunk] matrix written, scanned (r+w) and read back, ranges written
+        "binning": 2 * 12 * P + 4 * R + 16 * T * NC + 8 * T,
         "render_fwd": 52 * R + 28 * WH,               # id 4 B + 48-B record per instance; 28 B per pixel out
         "render_bwd": 52 * R + 2 * 48 * R + 24 * WH,  # + 48-B gradient record RMW per (tile, Gaussian)
         "preprocess_bwd": 190 * P,
@@ -159,8 +162,12 @@ def launches_per_step(T: int) -> int:
     """Kernel launches of one fwd+bwd (radix pass = hist + 3 scan + scatter)."""
     scan = 3
     rp = 1 + scan + 1
-    tile_passes = 2 if T > 256 else 1
-    return 1 + 4 * rp + scan + 1 + tile_passes * rp + 1 + 1 + 1 + 1
+    pre = 1 + 4 * rp + 1 + scan          # preprocess, depth argsort, rect gather, weight scan
+    if T <= 12288:                       # counting-sort binning: count walk, matrix scan, ranges, scatter walk
+        binning = 1 + scan + 1 + 1
+    else:                                # radix fallback: emit, 2 tile passes, ranges
+        binning = 1 + 2 * rp + 1
+    return pre + binning + 1 + 1 + 1     # + blend fwd, blend bwd, per-Gaussian bwd
 
 
 def run_ours(args, rank, world, local):
@@ -455,6 +462,90 @@ def sdf_leg(args, local, world=1, rank=0) -> dict:
                                  "traffic": TRAFFIC.get("sdf_query")}}}
 
 
+# ----------------------------------------------------------------------------------------------
+# Config C3 (BASELINE.json configs[2]): surfel rasterizer fwd+bwd (RGB + depth + normal) with fused-SSIM loss,
+# 1M surfels at 1920x1080, through the public autograd modules.  Reported under extra.surfel_ssim.
+C3 = dict(P=1_000_000, W=1920, H=1080, seed=1)
+
+
+def surfel_leg(args, local) -> dict:
+    from pings_b200 import synth
+    from pings_b200.diff_gaussian_surfel_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    from pings_b200.fused_ssim import fused_ssim
+    dev = torch.device("cuda", local)
+    P, W, H = C3["P"], C3["W"], C3["H"]
+    cam = synth.hd_camera(C3["seed"], W, H)
+    sc = {k: v.to(dev) for k, v in synth.surfels_in_view(cam, P, C3["seed"]).items()}
+    view, full, proj, center = [m.to(dev) for m in cam.matrices()]
+    g = torch.Generator().manual_seed(78)
+    target = torch.rand(3, H, W, generator=g).to(dev)
+    target_d = (torch.rand(1, H, W, generator=g) * 30 + 2).to(dev)
+    target_n = torch.nn.functional.normalize(torch.randn(3, H, W, generator=g), dim=0).to(dev)
+    cfg = torch.tensor([1, 1, 1, 1, 1], dtype=torch.float32, device=dev)
+    rs = GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, torch.zeros(3, device=dev), 1.0, view, full, proj,
+                                       torch.tensor([0.0, 0.0, H - 1.0, W - 1.0], device=dev),
+                                       torch.tensor([cam.cx / W, cam.cy / H], device=dev), 0, center, False, False, cfg)
+    rast = GaussianRasterizer(rs)
+    leaves = {k: sc[k].clone().requires_grad_(True) for k in sc}
+    theta = torch.zeros(1, 3, device=dev, requires_grad=True)
+    rho = torch.zeros(1, 3, device=dev, requires_grad=True)
+    m2d = torch.zeros(P, 3, device=dev, requires_grad=True)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    info = {}
+
+    def step():
+        for t in list(leaves.values()) + [theta, rho, m2d]:
+            t.grad = None
+        color, normal, depth, opac, radii, contrib = rast(leaves["means3D"], m2d, leaves["opacities"],
+                                                          colors_precomp=leaves["colors_precomp"],
+                                                          scales=leaves["scales"], rotations=leaves["rotations"],
+                                                          theta=theta, rho=rho)
+        l1 = (color - target).abs().mean()
+        loss = 0.8 * l1 + 0.2 * (1.0 - fused_ssim(color.unsqueeze(0), target.unsqueeze(0)))   # config.py:274
+        loss = loss + 0.02 * (depth - target_d).abs().mean() + 0.01 * (1 - (normal * target_n).sum(0)).mean() \
+            + 0.01 * opac.mean()
+        loss.backward()
+        info["vis"] = radii
+        return loss
+
+    steps, warm = max(3, min(args.steps, 10)), 3
+    for _ in range(warm):
+        step()
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(steps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step()
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in evs) / steps
+    # standalone fused SSIM fwd+bwd on [1,3,1080,1920] (24 + 28 B/element algorithmic)
+    img = torch.rand(1, 3, H, W, device=dev, requires_grad=True)
+    tgt = target.unsqueeze(0)
+    for _ in range(3):
+        img.grad = None
+        fused_ssim(img, tgt).backward()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(20):
+        img.grad = None
+        fused_ssim(img, tgt).backward()
+    b.record()
+    torch.cuda.synchronize()
+    ssim_ms = a.elapsed_time(b) / 20
+    pk = peaks()
+    ssim_gbs = 3 * H * W * (24 + 28) / (ssim_ms * 1e-3) / 1e9
+    return {"surfel_ssim": {"metric": "surfel raster fwd+bwd Mpix/s (RGB+depth+normal, fused-SSIM loss, C3)",
+                            "value": round(W * H / (ms * 1e-3) / 1e6, 2), "unit": "Mpix/s", "ms_per_step": round(ms, 4),
+                            "P": P, "W": W, "H": H, "visible": int((info["vis"] > 0).sum()),
+                            "note": "through GaussianRasterizer + fused_ssim autograd modules, loss and torch glue included",
+                            "ssim_fwd_bwd": {"ms": round(ssim_ms, 4), "gbs": round(ssim_gbs, 1),
+                                             "frac": round(ssim_gbs / pk["hbm_gbs"], 4), "alg_bytes_per_elem": 52}}}
+
+
 def sdf_cpu_leg(budget_s: float = 15.0) -> dict:
     """The reference's PyTorch CPU SDF path restated (oracle/neural_cpu.py) on this box's host cores."""
     from oracle import neural_cpu as O
@@ -509,6 +600,11 @@ def main():
         sdf = {"sdf": f"failed: {ex!r}"}
     if rank == 0:
         line.setdefault("extra", {}).update(sdf)
+        if world == 1:
+            try:
+                line["extra"].update(surfel_leg(args, local))
+            except Exception as ex:
+                line["extra"]["surfel_ssim"] = f"failed: {ex!r}"
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_baseline_line(args)
             if cb is not None:

@@ -127,3 +127,22 @@ def cotangents(cam: Camera, seed: int = 0, normal: bool = False) -> dict:
         out["normal"] = torch.randn(3, cam.H, cam.W, generator=g) / hw
         out["opac"] = torch.randn(1, cam.H, cam.W, generator=g) / hw
     return out
+
+
+def surfels_in_view(cam: Camera, P: int, seed: int = 1, facing: float = 0.7, **kw) -> dict:
+    """Config C3 scene: `gaussians_in_view(surfel=True)` with the quaternions re-oriented
+    so that about `facing` of the surfels face the camera (normal = third column of R, as in
+    RS forward.cu:274-276; a surfel is front-facing when dot(p - campos, n) < 0)."""
+    sc = gaussians_in_view(cam, P, seed, surfel=True, **kw)
+    g = torch.Generator().manual_seed(seed + 3000)
+    q = sc["rotations"]
+    w, x, y, z = q.unbind(1)
+    n = torch.stack([2 * (x * z + w * y), 2 * (y * z - w * x), 1 - 2 * (x * x + y * y)], dim=1)
+    campos = cam.T_wc[:3, 3].float()
+    back = ((sc["means3D"] - campos) * n).sum(1) > 0
+    frac_back = float(back.float().mean())
+    p_flip = 0.0 if frac_back <= 0 else max(0.0, min(1.0, (frac_back - (1.0 - facing)) / frac_back))
+    flip = back & (torch.rand(P, generator=g) < p_flip)
+    qf = torch.stack([-x, w, z, -y], dim=1)  # q * (0,1,0,0): half turn about the local x axis flips the normal
+    sc["rotations"] = torch.where(flip[:, None], qf, q).contiguous()
+    return sc
