@@ -73,7 +73,7 @@ inline size_t carve_geom(int variant, int P, void* base, GeomWs* ws) {
   w.sorted_idx = c.take<uint32_t>(p);
   w.offsets = c.take<uint32_t>(p);
   w.clamped = c.take<uint8_t>(3 * p);
-  w.sort_scratch = c.take<uint32_t>(sort_scratch_elems(p));
+  w.sort_scratch = c.take<uint32_t>(depth_sort_scratch_elems(p));
   w.total = c.take<unsigned long long>(2);
   w.tau_acc = c.take<double>(8);
   w.gacc_count = (variant == PG_VARIANT_SURFEL ? 4 : 3) * p;
@@ -385,6 +385,16 @@ __global__ void __launch_bounds__(256) gather_rect_kernel(int P, const uint32_t*
 inline cudaError_t depth_order_and_offsets(const GeomWs& ws, int P, bool fast, cudaStream_t st) {
   cudaError_t e;
   const uint32_t n = (uint32_t)P;
+  const uint32_t nblk = sort_num_blocks(n);
+  if (depth_sort_coop_fits(nblk)) {
+    DepthSortArgs a;
+    a.dkey = ws.dkey; a.keyA = ws.keyA; a.valA = ws.valA; a.keyB = ws.keyB; a.valB = ws.sorted_idx;
+    a.hist = ws.sort_scratch; a.bsum = ws.sort_scratch + (size_t)2 * nblk * 256;
+    a.wsrc = fast ? ws.wts : ws.tiles; a.rect = ws.rect; a.srect = ws.srect; a.offsets = ws.offsets;
+    a.total_out = fast ? ws.wtotal : nullptr;
+    a.n = n; a.nblk = nblk;
+    return depth_sort_coop(a, st);
+  }
   // 4 stable passes, 8 bits each: (dkey,iota)->(A,valA)->(B,sorted)->(A,valA)->(-,sorted)
   e = radix_pass<uint32_t, true, true>(ws.dkey, nullptr, ws.keyA, ws.valA, n, 0, 8, ws.sort_scratch, st);
   if (e != cudaSuccess) return e;

@@ -9,6 +9,7 @@
 // arrive in long equal runs, so plain shared atomics would serialise).
 #pragma once
 #include "pg_common.cuh"
+#include <cooperative_groups.h>
 
 namespace pg {
 
@@ -270,6 +271,169 @@ inline cudaError_t radix_pass(const KeyT* kin, const uint32_t* vin, KeyT* kout, 
   radix_scatter_kernel<KeyT, IOTA, WRITE_KEYS><<<nblk, kSortThreads, 0, st>>>(
       kin, vin, kout, vout, n, shift, nbins, hist, nblk);
   return cudaGetLastError();
+}
+
+// ---- fused depth argsort (one cooperative launch) ---------------------------------------------
+// The P-sized depth sort is latency bound (32 MB of traffic, but 12 launches + 4 three-kernel scans
+// when run pass by pass).  For P <= kCoopSortMaxBlocks * 4096 the four LSD passes, the depth-order
+// gather of the tile rects and the exclusive scan of the binning weights run as ONE cooperative
+// kernel: a CTA keeps its 4096 (key, value) pairs in registers between the counting and the scatter
+// half of a pass, the [block][digit] histogram matrix stays in L2 and every CTA derives its own 256
+// scatter bases from it (column sum below its row + digit prefix of the column totals), so a pass
+// costs two grid barriers and no scan kernels.
+constexpr uint32_t kCoopSortMaxBlocks = 296;  // 2 CTAs per SM; above this every CTA re-reading the matrix dominates
+
+struct DepthSortArgs {
+  const uint32_t* dkey;   // [n] keys (read only)
+  uint32_t* keyA;         // ping
+  uint32_t* valA;
+  uint32_t* keyB;         // pong (keys of the last pass are never written)
+  uint32_t* valB;         // final argsort
+  uint32_t* hist;         // [2][nblk][256] double-buffered histogram matrix
+  uint32_t* bsum;         // [nblk] tail scan block sums
+  const uint32_t* wsrc;   // [n] per-item weight, gathered through the argsort
+  const uint2* rect;      // [n] per-item rect, gathered through the argsort
+  uint2* srect;           // [n] out
+  uint32_t* offsets;      // [n] out: exclusive scan of wsrc in sorted order
+  uint32_t* total_out;    // nullable: grand total of wsrc
+  uint32_t n, nblk;
+};
+
+inline size_t depth_sort_scratch_elems(uint64_t n) {
+  const size_t nblk = sort_num_blocks(n);
+  const size_t coop = 2 * nblk * 256 + nblk + 64;
+  const size_t plain = sort_scratch_elems(n);
+  return coop > plain ? coop : plain;
+}
+
+__global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const DepthSortArgs a) {
+  namespace cg = cooperative_groups;
+  cg::grid_group grid = cg::this_grid();
+  __shared__ uint32_t wh[kSortWarps][256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t blk = blockIdx.x, n = a.n, nblk = a.nblk;
+  const uint32_t base = blk * kSortChunk + warp * kSortWarpItems;
+  const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll 1
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = pass * 8;
+    const uint32_t* kin = pass == 0 ? a.dkey : ((pass & 1) ? a.keyA : a.keyB);
+    const uint32_t* vin = (pass & 1) ? a.valA : a.valB;
+    uint32_t* kout = (pass & 1) ? a.keyB : a.keyA;
+    uint32_t* vout = (pass & 1) ? a.valB : a.valA;
+    uint32_t* hist = a.hist + (size_t)(pass & 1) * nblk * 256;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) wh[w][threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t k[kSortIpt], v[kSortIpt];
+#pragma unroll
+    for (int it = 0; it < kSortIpt; ++it) {
+      const uint32_t i = base + it * 32 + lane;
+      // .cg: pass >= 1 reads what other CTAs wrote earlier in this launch
+      k[it] = i < n ? __ldcg(kin + i) : 0u;
+      v[it] = i < n ? (pass == 0 ? i : __ldcg(vin + i)) : 0u;
+    }
+#pragma unroll
+    for (int it = 0; it < kSortIpt; ++it) {
+      const uint32_t i = base + it * 32 + lane;
+      const uint32_t d = i < n ? ((k[it] >> shift) & 255u) : 0xffffffffu;
+      const uint32_t peers = __match_any_sync(0xffffffffu, d);
+      if (d != 0xffffffffu && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
+      __syncwarp();
+    }
+    __syncthreads();
+    {
+      uint32_t c = 0;
+#pragma unroll
+      for (int w = 0; w < kSortWarps; ++w) c += wh[w][threadIdx.x];
+      hist[(size_t)blk * 256 + threadIdx.x] = c;
+    }
+    grid.sync();
+    {
+      // digit = threadIdx.x: items of this digit in earlier blocks, and in all blocks
+      uint32_t below = 0, all = 0;
+#pragma unroll 8
+      for (uint32_t b = 0; b < nblk; ++b) {
+        const uint32_t x = __ldcg(hist + (size_t)b * 256 + threadIdx.x);
+        all += x;
+        below += b < blk ? x : 0u;
+      }
+      uint32_t tot;
+      uint32_t run = block_excl_scan_256(all, &tot) + below;
+#pragma unroll
+      for (int w = 0; w < kSortWarps; ++w) {
+        const uint32_t c = wh[w][threadIdx.x];
+        wh[w][threadIdx.x] = run;
+        run += c;
+      }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < kSortIpt; ++it) {
+      const uint32_t i = base + it * 32 + lane;
+      const bool valid = i < n;
+      const uint32_t d = valid ? ((k[it] >> shift) & 255u) : 0xffffffffu;
+      const uint32_t peers = __match_any_sync(0xffffffffu, d);
+      if (valid) {
+        const uint32_t pos = wh[warp][d] + __popc(peers & lt);
+        if (pass < 3) kout[pos] = k[it];
+        vout[pos] = v[it];
+      }
+      __syncwarp();
+      if (valid && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
+      __syncwarp();
+    }
+    grid.sync();
+  }
+  // tail: srect[i] = rect[sorted[i]]; offsets = exclusive scan of wsrc[sorted[i]]
+  const uint32_t tbase = blk * kSortChunk + threadIdx.x * kSortIpt;
+  uint32_t pre[kSortIpt];
+  uint32_t s = 0;
+#pragma unroll
+  for (int q = 0; q < kSortIpt; ++q) {
+    const uint32_t i = tbase + q;
+    uint32_t x = 0;
+    if (i < n) {
+      const uint32_t id = __ldcg(a.valB + i);
+      a.srect[i] = a.rect[id];
+      x = a.wsrc[id];
+    }
+    pre[q] = s;
+    s += x;
+  }
+  uint32_t mine;
+  const uint32_t ex = block_excl_scan_256(s, &mine);
+  if (threadIdx.x == 0) a.bsum[blk] = mine;
+  grid.sync();
+  uint32_t part = 0;
+  for (uint32_t b = threadIdx.x; b < blk; b += kSortThreads) part += __ldcg(a.bsum + b);
+  uint32_t before;
+  block_excl_scan_256(part, &before);
+#pragma unroll
+  for (int q = 0; q < kSortIpt; ++q) {
+    const uint32_t i = tbase + q;
+    if (i < n) a.offsets[i] = pre[q] + ex + before;
+  }
+  if (a.total_out && blk == nblk - 1 && threadIdx.x == 0) *a.total_out = before + mine;
+}
+
+// True when the cooperative kernel can hold all `nblk` CTAs resident on the current device.
+inline bool depth_sort_coop_fits(uint32_t nblk) {
+  static int capacity = -1;  // per process; every rank drives one device
+  if (capacity < 0) {
+    int dev = 0, sms = 0, per_sm = 0, coop = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, depth_sort_coop_kernel, kSortThreads, 0);
+    capacity = coop ? sms * per_sm : 0;
+  }
+  return nblk > 0 && nblk <= kCoopSortMaxBlocks && (int)nblk <= capacity;
+}
+
+inline cudaError_t depth_sort_coop(DepthSortArgs a, cudaStream_t st) {
+  void* params[] = {(void*)&a};
+  return cudaLaunchCooperativeKernel((const void*)depth_sort_coop_kernel, dim3(a.nblk), dim3(kSortThreads), params, 0, st);
 }
 
 }  // namespace pg
