@@ -153,17 +153,28 @@ def algorithmic_bytes(P: int, R: int, W: int, H: int) -> dict:
         # chunked counting sort: two walks over (id 4 B + rect 8 B) per Gaussian, one 4-B id
         # write per instance, [tile][chunk] matrix written, scanned (r+w) and read back, ranges written
         "binning": 2 * 12 * P + 4 * R + 16 * T * NC + 8 * T,
-        "render_fwd": 52 * R + 28 * WH,               # id 4 B + 48-B record per instance; 28 B per pixel out
-        "render_bwd": 52 * R + 2 * 48 * R + 24 * WH,  # + 48-B gradient record RMW per (tile, Gaussian)
+        # blend kernels: HBM sees the id list once, each record once (re-reads by other tiles hit L2) and the
+        # images; the per-instance record / gradient traffic (L2_BYTES below) is L2 and shared-memory work
+        "render_fwd": 4 * R + 48 * P + 28 * WH,
+        "render_bwd": 4 * R + 48 * P + 2 * 48 * P + 52 * WH,
         "preprocess_bwd": 190 * P,
     }
 
 
-def launches_per_step(T: int) -> int:
+def l2_bytes(P: int, R: int) -> dict:
+    """Per-launch L2-level traffic of the blend kernels: 4-B id + 48-B record per (tile, Gaussian) instance,
+    plus the 48-B gradient record accumulated with atomics per instance in the backward."""
+    return {"render_fwd": 52 * R, "render_bwd": 52 * R + 48 * R}
+
+
+def launches_per_step(T: int, P: int) -> int:
     """Kernel launches of one fwd+bwd (radix pass = hist + 3 scan + scatter)."""
     scan = 3
     rp = 1 + scan + 1
-    pre = 1 + 4 * rp + 1 + scan          # preprocess, depth argsort, rect gather, weight scan
+    if (P + 4095) // 4096 <= 296:        # one cooperative launch: 4 LSD passes + rect gather + weight scan
+        pre = 1 + 1
+    else:
+        pre = 1 + 4 * rp + 1 + scan      # preprocess, depth argsort, rect gather, weight scan
     if T <= 12288:                       # counting-sort binning: count walk, matrix scan, ranges, scatter walk
         binning = 1 + scan + 1 + 1
     else:                                # radix fallback: emit, 2 tile passes, ranges
@@ -232,8 +243,31 @@ def run_ours(args, rank, world, local):
     rs = GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, bg, 1.0, view, full, proj, 0, center, False, False)
     rast = GaussianRasterizer(rs)
 
-    def step_e2e():
-        leaves = {k: pinned[k].to(dev, non_blocking=True).requires_grad_(True) for k in pinned}
+    # Double-buffered input staging: the H2D copy of step k+1 runs on a copy stream while step k computes
+    # (every copy is inside the timed region; only the first one is exposed).
+    copy_stream = torch.cuda.Stream(device=dev)
+    slots = [{k: torch.empty_like(v, device=dev) for k, v in pinned.items()} for _ in range(2)]
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+
+    def upload(i: int):
+        slot = i & 1
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[slot])
+            for k, v in pinned.items():
+                slots[slot][k].copy_(v, non_blocking=True)
+            ready[slot].record(copy_stream)
+
+    def step_e2e(i: int, prefetch: bool, more: bool = True):
+        cur = torch.cuda.current_stream()
+        if prefetch:
+            if more:
+                upload(i + 1)                  # overlaps this step's kernels
+        else:
+            upload(i)                          # serial variant: copy, then compute
+        slot = i & 1
+        cur.wait_event(ready[slot])
+        leaves = {k: slots[slot][k].detach().requires_grad_(True) for k in pinned}
         theta = torch.zeros(1, 3, device=dev, requires_grad=True)
         rho = torch.zeros(1, 3, device=dev, requires_grad=True)
         m2d = torch.zeros(P, 3, device=dev, requires_grad=True)
@@ -242,30 +276,48 @@ def run_ours(args, rank, world, local):
                                                        rotations=leaves["rotations"], theta=theta, rho=rho)
         loss = (color - target).abs().mean() + 0.01 * depth.mean()
         loss.backward()
+        consumed[slot].record(cur)
         if world > 1:
             torch.cat([leaves[k].grad.flatten() for k in ("means3D", "colors_precomp", "opacities", "scales", "rotations")],
                       out=grads_flat)
             dist.all_reduce(grads_flat)
         res = torch.cat([loss.detach().view(1), rho.grad.flatten(), theta.grad.flatten()])
         host_out.copy_(res, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        cur.synchronize()
         return float(host_out[0])
 
-    for _ in range(args.warmup):
-        step_e2e()
-    barrier(world)
-    e2e_ms = 0.0
-    for _ in range(args.steps):
-        flush.fill_(1)
+    def run_e2e(prefetch: bool) -> float:
+        """K steps back to back, wall clock from the first upload to the last result on the host; the
+        L2 flush between steps is inside the timed region (about 0.04 ms per step)."""
+        for ev in consumed:
+            ev.record()
+        for i in range(args.warmup):
+            if prefetch and i == 0:
+                upload(0)
+            step_e2e(i, prefetch, more=i + 1 < args.warmup)
+        torch.cuda.synchronize()
+        barrier(world)
+        first = args.warmup
+        for ev in consumed:
+            ev.record()
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        step_e2e()
-        e2e_ms += (time.perf_counter() - t0) * 1e3
-    t = torch.tensor([e2e_ms], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_ms_per_step = float(t.item()) / args.steps
+        if prefetch:
+            upload(first)
+        for i in range(first, first + args.steps):
+            flush.fill_(1)
+            step_e2e(i, prefetch, more=i + 1 < first + args.steps)
+        torch.cuda.synchronize()
+        ms = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()) / args.steps
+
+    e2e_serial_ms = run_e2e(False)
+    e2e_ms_per_step = run_e2e(True)
     e2e_value = world * W * H / (e2e_ms_per_step * 1e-3) / 1e6
+    e2e_serial_value = world * W * H / (e2e_serial_ms * 1e-3) / 1e6
 
     # ---- per-phase attribution (separate pass; events on the launching stream) ----
     phases: dict[str, list[float]] = {}
@@ -288,6 +340,10 @@ def run_ours(args, rank, world, local):
     per_phase = {k: dict(ms=round(phase_ms[k], 4), alg_bytes=ab[k],
                          gbs=round(ab[k] / (phase_ms[k] * 1e-3) / 1e9, 1),
                          frac=round(ab[k] / (phase_ms[k] * 1e-3) / 1e9 / pk["hbm_gbs"], 4)) for k in phase_ms}
+    for k, b in l2_bytes(P, R).items():
+        if k in per_phase:
+            per_phase[k]["l2_bytes"] = b
+            per_phase[k]["l2_gbs"] = round(b / (phase_ms[k] * 1e-3) / 1e9, 1)
     T = ((W + 15) // 16) * ((H + 15) // 16)
     line = {
         "metric": "raster fwd+bwd Mpix/s (3DGS, pose grads)", "value": round(value, 2), "unit": "Mpix/s",
@@ -300,8 +356,11 @@ def run_ours(args, rank, world, local):
                    "exchange": "NCCL all-reduce of Gaussian-parameter grads (28 MB)" if world > 1 else "none (N=1)"},
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 2), "unit": "Mpix/s", "ms_per_step": round(e2e_ms_per_step, 4),
-                "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 28},
-        "gpu_launches": launches_per_step(T) * args.steps,
+                "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 28,
+                "staging": "double-buffered: H2D of step k+1 on a copy stream overlaps step k; L2 flush between steps "
+                           "inside the timed region",
+                "serial_value": round(e2e_serial_value, 2), "serial_ms_per_step": round(e2e_serial_ms, 4)},
+        "gpu_launches": launches_per_step(T, P) * args.steps,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": round(achieved / pk["hbm_gbs"], 4), "traffic": TRAFFIC.get(dom),
                      "peak_source": pk["source"], "phases": per_phase},

@@ -18,6 +18,7 @@
 #pragma once
 #include "pg_common.cuh"
 #include "pg_sort.cuh"
+#include "pg_bin_band.cuh"
 
 namespace pg {
 
@@ -129,6 +130,7 @@ struct BinWs {
   uint32_t* scratch; // radix scratch for R items   (radix path only)
   uint32_t* matrix;  // [tiles * chunks + 1] count -> offset matrix, tile-major (counting path)
   uint32_t* mscan;   // scan scratch for the matrix
+  BandWs band;       // band binning (pg_bin_band.cuh), the default path
 };
 
 inline size_t carve_binning(int64_t R, int W, int H, void* base, BinWs* ws) {
@@ -136,8 +138,20 @@ inline size_t carve_binning(int64_t R, int W, int H, void* base, BinWs* ws) {
   BinWs w;
   memset(&w, 0, sizeof(w));
   size_t r = (size_t)(R > 0 ? R : 1);
-  const int T = div_up(W, kTile) * div_up(H, kTile);
-  if (bin_fast_path(T)) {
+  const int gx = div_up(W, kTile), gy = div_up(H, kTile);
+  const int T = gx * gy;
+  if (band_path(gx, gy)) {
+    const int nL = band_lists(gx, gy);
+    const size_t nA = (size_t)nL * band_row_chunks(nL) + 1, nB = band_tilemat_bound(R, nL);
+    w.valA = c.take<uint32_t>(r);
+    w.band.recs = c.take<uint32_t>(r);
+    w.band.matA = c.take<uint32_t>(nA);
+    w.band.lstart = c.take<uint32_t>(nL + 1);
+    w.band.segbase = c.take<uint32_t>(nL + 1);
+    w.band.scan_len = c.take<uint32_t>(4);
+    w.band.tilemat = c.take<uint32_t>(nB);
+    w.band.mscan = c.take<uint32_t>(scan_scratch_elems(nA > nB ? nA : nB) + 64);
+  } else if (bin_fast_path(T)) {
     w.valA = c.take<uint32_t>(r);
     const size_t m = (size_t)T * bin_max_chunks(T) + 1;
     w.matrix = c.take<uint32_t>(m);
@@ -418,6 +432,7 @@ inline cudaError_t bin_instances(const GeomWs& g, const BinWs& b, const ImageWs&
   if (e != cudaSuccess) return e;
   *point_list = b.valA;
   if (R <= 0 || P <= 0) return cudaSuccess;
+  if (band_path(gx, gy)) return band_bin(b.band, P, gx, gy, R, g.sorted_idx, g.srect, g.rect, b.valA, im.ranges, st);
   if (bin_fast_path(T)) {
     const int nchunks = bin_max_chunks(T);
     const int wpc = bin_warps_per_cta(T);
@@ -462,7 +477,7 @@ inline cudaError_t bin_instances(const GeomWs& g, const BinWs& b, const ImageWs&
 
 inline const uint32_t* sorted_point_list(const BinWs& b, int W, int H) {
   const int T = div_up(W, kTile) * div_up(H, kTile);
-  if (bin_fast_path(T)) return b.valA;
+  if (band_path(div_up(W, kTile), div_up(H, kTile)) || bin_fast_path(T)) return b.valA;
   return tile_sort_passes(T) == 2 ? b.valA : b.valB;
 }
 

@@ -52,7 +52,8 @@ __device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* to
 template <bool GATHER>
 __global__ void __launch_bounds__(kScanThreads) scan_reduce_kernel(
     const uint32_t* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t n,
-    uint32_t* __restrict__ block_sums) {
+    uint32_t* __restrict__ block_sums, const uint32_t* __restrict__ n_dev = nullptr) {
+  if (n_dev) n = min(n, *n_dev);   // device-side length (<= the launch bound n)
   const uint32_t base = blockIdx.x * kScanChunk;
   uint32_t s = 0;
 #pragma unroll
@@ -106,7 +107,12 @@ __global__ void __launch_bounds__(1024) scan_sums_kernel(uint32_t* __restrict__ 
 template <bool GATHER>
 __global__ void __launch_bounds__(kScanThreads) scan_down_kernel(
     const uint32_t* __restrict__ in, const uint32_t* __restrict__ idx, uint32_t n,
-    const uint32_t* __restrict__ block_sums, uint32_t* __restrict__ out) {
+    const uint32_t* __restrict__ block_sums, uint32_t* __restrict__ out,
+    const uint32_t* __restrict__ n_dev = nullptr) {
+  if (n_dev) {
+    n = min(n, *n_dev);
+    if (blockIdx.x * kScanChunk >= n) return;   // uniform per block
+  }
   // thread t owns items [base + t*16, base + t*16 + 16)
   const uint32_t base = blockIdx.x * kScanChunk + threadIdx.x * kScanIpt;
   uint32_t v[kScanIpt];
@@ -146,6 +152,18 @@ inline cudaError_t exclusive_scan_u32(const uint32_t* in, const uint32_t* idx, u
   scan_sums_kernel<<<1, 1024, 0, st>>>(scratch, nblk, total_out);
   if (idx) scan_down_kernel<true><<<nblk, kScanThreads, 0, st>>>(in, idx, n, scratch, out);
   else     scan_down_kernel<false><<<nblk, kScanThreads, 0, st>>>(in, idx, n, scratch, out);
+  return cudaGetLastError();
+}
+
+// In-place exclusive scan whose true length *n_dev (<= n_bound) is only known on the device: the grid
+// is sized for n_bound, blocks past the true length contribute 0 and write nothing.
+inline cudaError_t exclusive_scan_u32_dyn(uint32_t* data, uint32_t n_bound, const uint32_t* n_dev,
+                                          uint32_t* scratch, cudaStream_t st) {
+  if (n_bound == 0) return cudaSuccess;
+  const uint32_t nblk = (n_bound + kScanChunk - 1) / kScanChunk;
+  scan_reduce_kernel<false><<<nblk, kScanThreads, 0, st>>>(data, nullptr, n_bound, scratch, n_dev);
+  scan_sums_kernel<<<1, 1024, 0, st>>>(scratch, nblk, nullptr);
+  scan_down_kernel<false><<<nblk, kScanThreads, 0, st>>>(data, nullptr, n_bound, scratch, data, n_dev);
   return cudaGetLastError();
 }
 
