@@ -25,6 +25,7 @@ constexpr int kBandMaxLists = 1024;   // [row][band] lists; more -> older paths
 constexpr int kBandSegRecs = 128;     // records per warp segment in stage B
 constexpr int kBandStageCap = 2048;   // staged instances per warp (8 KB)
 constexpr int kBandWarps = 8;
+constexpr int kBandStageWords = kBandStageCap + 32 + kBandStageCap / 4;   // ids + deltas + tile bytes
 
 inline int band_count(int gx) { return (gx + kBandTiles - 1) / kBandTiles; }
 inline int band_lists(int gx, int gy) { return band_count(gx) * gy; }
@@ -136,6 +137,31 @@ __global__ void __launch_bounds__(1024) band_header_kernel(int nL, int nchunks, 
   }
 }
 
+// Lane t appends the ids of the records (one per lane, coverage mask cm) that cover its tile, in lane
+// order, to its run of the stage starting at k; returns the advanced k.
+__device__ __forceinline__ uint32_t band_stage_group(uint32_t cm, uint32_t id, uint32_t lane_bit, int lane,
+                                                     uint32_t* stage, uint8_t* stage_tile, uint32_t k) {
+#pragma unroll
+  for (int jj = 0; jj < 32; ++jj) {
+    const bool hit = (__shfl_sync(0xffffffffu, cm, jj) & lane_bit) != 0u;
+    const uint32_t idj = __shfl_sync(0xffffffffu, id, jj);
+    if (hit) {
+      stage[k] = idj;
+      stage_tile[k] = (uint8_t)lane;
+      ++k;
+    }
+  }
+  return k;
+}
+
+// Flat flush: the stage is tile-major, so consecutive lanes write consecutive words of a run.
+__device__ __forceinline__ void band_flush(const uint32_t* stage, const uint8_t* stage_tile, const uint32_t* stage_delta,
+                                           uint32_t tot, int lane, uint32_t* __restrict__ out) {
+  __syncwarp();
+  for (uint32_t q = lane; q < tot; q += 32) out[q + stage_delta[stage_tile[q]]] = stage[q];
+  __syncwarp();
+}
+
 // ---- stage B ------------------------------------------------------------------------------------
 // Persistent warps stride over the segments.  Lane t owns tile `band*32 + t`.
 template <bool WRITE>
@@ -147,7 +173,10 @@ __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   uint32_t* sb = band_sm;                                      // [nL + 1]
   const int sb_words = (nL + 1 + 31) & ~31;
-  uint32_t* stage = band_sm + sb_words + warp * kBandStageCap;  // WRITE only
+  // WRITE only: per warp [cap] ids, [32] run deltas, [cap] owning tile (bytes)
+  uint32_t* stage = band_sm + sb_words + warp * kBandStageWords;
+  uint32_t* stage_delta = stage + kBandStageCap;
+  uint8_t* stage_tile = reinterpret_cast<uint8_t*>(stage_delta + 32);
   for (int k = threadIdx.x; k <= nL; k += blockDim.x) sb[k] = segbase[k];
   __syncthreads();
   const uint32_t S = sb[nL];
@@ -171,44 +200,40 @@ __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
       const uint32_t inc = warp_incl_scan(c, lane);
       start = inc - c;
       staged = __shfl_sync(0xffffffffu, inc, 31) <= (uint32_t)kBandStageCap;
-      k = staged ? start : goff;
+      k = staged ? start : 0u;
     }
+    const uint32_t lane_bit = 1u << lane;
     for (uint32_t j0 = 0; j0 < n; j0 += 32) {
-      uint32_t id = 0, pk = 0;   // pk = x0 | width << 8 relative to the band; 0 -> covers nothing
+      uint32_t id = 0, cm = 0;   // cm = coverage mask of this lane's record over the band's 32 tiles
       if (j0 + lane < n) {
         id = rp[j0 + lane];
         const uint32_t rx = rect[id].x;
         const uint32_t x0 = max(rx & 0xffffu, band0) - band0;
-        const uint32_t x1 = min(rx >> 16, band0 + kBandTiles) - band0;
-        pk = x0 | ((x1 - x0) << 8);
+        const uint32_t x1 = min(rx >> 16, band0 + kBandTiles) - band0;   // 1..32
+        cm = (0xffffffffu >> (32u - (x1 - x0))) << x0;
       }
+      if (!WRITE) {
 #pragma unroll
-      for (int jj = 0; jj < 32; ++jj) {
-        const uint32_t p = __shfl_sync(0xffffffffu, pk, jj);
-        const bool hit = ((uint32_t)lane - (p & 0xffu)) < (p >> 8);
-        if (WRITE) {
-          const uint32_t idj = __shfl_sync(0xffffffffu, id, jj);
-          if (hit) {
-            if (staged) stage[k] = idj; else out[k] = idj;
-            ++k;
-          }
-        } else {
-          c += hit ? 1u : 0u;
-        }
+        for (int jj = 0; jj < 32; ++jj) c += (__shfl_sync(0xffffffffu, cm, jj) & lane_bit) ? 1u : 0u;
+      } else if (staged) {
+        k = band_stage_group(cm, id, lane_bit, lane, stage, stage_tile, k);
+      } else {
+        // dense segment (> cap instances): stage and flush these 32 records on their own (<= 1024 instances)
+        uint32_t cg = 0;
+#pragma unroll
+        for (int jj = 0; jj < 32; ++jj) cg += (__shfl_sync(0xffffffffu, cm, jj) & lane_bit) ? 1u : 0u;
+        const uint32_t inc = warp_incl_scan(cg, lane);
+        band_stage_group(cm, id, lane_bit, lane, stage, stage_tile, inc - cg);
+        stage_delta[lane] = goff + k - (inc - cg);   // k = instances of this tile already written
+        band_flush(stage, stage_tile, stage_delta, __shfl_sync(0xffffffffu, inc, 31), lane, out);
+        k += cg;
       }
     }
     if (!WRITE) {
       tilemat[e] = c;
     } else if (staged) {
-      __syncwarp();
-#pragma unroll 4
-      for (int x = 0; x < kBandTiles; ++x) {
-        const uint32_t nx = __shfl_sync(0xffffffffu, c, x);
-        const uint32_t st = __shfl_sync(0xffffffffu, start, x);
-        const uint32_t go = __shfl_sync(0xffffffffu, goff, x);
-        for (uint32_t q = lane; q < nx; q += 32) out[go + q] = stage[st + q];
-      }
-      __syncwarp();
+      stage_delta[lane] = goff - start;   // staged position -> output position, for this lane's tile
+      band_flush(stage, stage_tile, stage_delta, __shfl_sync(0xffffffffu, start + c, 31), lane, out);
     }
   }
 }
@@ -237,7 +262,7 @@ inline cudaError_t band_bin(const BandWs& w, int P, int gx, int gy, int64_t R, c
   const size_t smA = (size_t)kBandWarps * nL * sizeof(uint32_t);
   const int sb_words = (nL + 1 + 31) & ~31;
   const size_t smC = (size_t)sb_words * sizeof(uint32_t);
-  const size_t smW = smC + (size_t)kBandWarps * kBandStageCap * sizeof(uint32_t);
+  const size_t smW = smC + (size_t)kBandWarps * kBandStageWords * sizeof(uint32_t);
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(band_expand_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
@@ -269,7 +294,7 @@ inline cudaError_t band_bin(const BandWs& w, int P, int gx, int gy, int64_t R, c
   e = exclusive_scan_u32_dyn(w.tilemat, (uint32_t)band_tilemat_bound(R, nL), w.scan_len, w.mscan, st);
   if (e != cudaSuccess) return e;
   band_ranges_kernel<<<(T + 255) / 256, 256, 0, st>>>(T, gx, NB, w.segbase, w.tilemat, ranges);
-  band_expand_kernel<true><<<sms * 3, kBandWarps * 32, smW, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect,
+  band_expand_kernel<true><<<sms * 2, kBandWarps * 32, smW, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect,
                                                                    w.tilemat, out);
   return cudaGetLastError();
 }
