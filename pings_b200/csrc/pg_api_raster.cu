@@ -77,6 +77,7 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
   const int W = prm->image_width, H = prm->image_height;
   const int gx = div_up(W, kTile), gy = div_up(H, kTile);
   if ((int64_t)gx * gy > 65535) return PG_ERR_UNSUPPORTED;
+  if (P >= (1 << kBandIdBits)) return PG_ERR_UNSUPPORTED;   // band binning tags ids with 5 tile bits
   if (geom_bytes < carve_geom(prm->variant, P, nullptr, nullptr)) return PG_ERR_WORKSPACE;
   cudaStream_t st = (cudaStream_t)stream;
   int rc = ensure_slot();

@@ -25,7 +25,8 @@ constexpr int kBandMaxLists = 1024;   // [row][band] lists; more -> older paths
 constexpr int kBandSegRecs = 128;     // records per warp segment in stage B
 constexpr int kBandStageCap = 2048;   // staged instances per warp (8 KB)
 constexpr int kBandWarps = 8;
-constexpr int kBandStageWords = kBandStageCap + 32 + kBandStageCap / 4;   // ids + deltas + tile bytes
+constexpr int kBandStageWords = kBandStageCap + 32;   // staged words + run deltas
+constexpr int kBandIdBits = 27;       // staged word = owning lane << 27 | Gaussian id  (P < 2^27)
 
 inline int band_count(int gx) { return (gx + kBandTiles - 1) / kBandTiles; }
 inline int band_lists(int gx, int gy) { return band_count(gx) * gy; }
@@ -37,32 +38,41 @@ inline int band_row_chunks(int nL) {
 }
 // upper bounds used to size the workspace from num_rendered alone (records <= instances)
 inline size_t band_seg_bound(int64_t R, int nL) { return (size_t)(R > 0 ? R : 0) / kBandSegRecs + (size_t)nL; }
-inline size_t band_tilemat_bound(int64_t R, int nL) { return band_seg_bound(R, nL) * kBandTiles + 1; }
+inline size_t band_tilemat_bound(int64_t R, int nL) { return band_seg_bound(R, nL) * kBandTiles; }
 
 struct BandWs {
-  uint32_t* recs;      // [<= R] Gaussian ids, list-major, depth-ordered inside a list
-  uint32_t* matA;      // [nL * chunks + 1] stage-A counts -> record offsets
-  uint32_t* lstart;    // [nL + 1] first record of list l (lstart[nL] = number of records)
-  uint32_t* segbase;   // [nL + 1] first segment of list l (segbase[nL] = number of segments)
-  uint32_t* scan_len;  // [1] 32 * segments + 1
-  uint32_t* tilemat;   // [32 * segments + 1] stage-B counts -> output offsets; index 32*segbase[l] + x*nseg_l + s
-  uint32_t* mscan;     // scan scratch
+  uint32_t* recs;       // [<= R] Gaussian ids, list-major, depth-ordered inside a list
+  uint32_t* matA;       // [nL][chunks] stage-A counts -> exclusive prefix inside the list
+  uint32_t* lcount;     // [nL] records per list
+  uint32_t* lstart;     // [nL + 1] first record of list l (lstart[nL] = number of records)
+  uint32_t* segbase;    // [nL + 1] first segment of list l (segbase[nL] = number of segments)
+  uint32_t* tilemat;    // [32 * segments] stage-B counts -> exclusive prefix inside the tile;
+                        // index 32*segbase[l] + x*nseg_l + s
+  uint32_t* tiletot;    // [nL * 32] instances per tile slot (list l, lane x)
+  uint32_t* tilestart;  // [nL * 32] first output position of the tile slot
+  uint32_t* ticket;     // [2] last-block-done counters of the two scan kernels (zeroed per call)
 };
 
 // ---- stage A ----------------------------------------------------------------------------------
-// One warp per chunk of `per_warp` consecutive depth ranks; `cur` = per-warp counters/cursors of
-// all lists in shared memory.  For 32 Gaussians at a time the warp loops over the (row, band)
-// cells of their joint bounding box and ballots coverage: a cell's 32-bit mask gives both the count
-// and, in the WRITE pass, the stable rank of every covering lane.
+// One warp per chunk of `per_warp` consecutive depth ranks; per-warp shared memory holds the
+// counters/cursors of all lists (`cur`) and, for the 32 Gaussians in flight, one coverage ballot
+// per tile row (`Rm`) and per band (`Bm`): the cell (row r, band b) is covered by the lanes
+// Rm[r] & Bm[b].  Counting is cell-parallel (a lane per cell, popc of the mask); in the WRITE pass
+// every lane walks its own cells and stores its id at cursor + (number of covering lanes below it),
+// which keeps a list depth-ordered, then the cursors advance cell-parallel.
 template <bool WRITE>
 __global__ void __launch_bounds__(kBandWarps * 32) band_rows_kernel(
-    int P, int per_warp, int NB, int nL, int nchunks, const uint32_t* __restrict__ sorted_idx,
-    const uint2* __restrict__ srect, uint32_t* __restrict__ matA, uint32_t* __restrict__ recs) {
+    int P, int per_warp, int NB, int GY, int nchunks, const uint32_t* __restrict__ sorted_idx,
+    const uint2* __restrict__ srect, uint32_t* __restrict__ matA, const uint32_t* __restrict__ lstart,
+    uint32_t* __restrict__ recs) {
   extern __shared__ uint32_t band_sm[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int chunk = blockIdx.x * kBandWarps + warp;
-  uint32_t* cur = band_sm + (size_t)warp * nL;
-  for (int l = lane; l < nL; l += 32) cur[l] = WRITE ? matA[(size_t)l * nchunks + chunk] : 0u;
+  const int nL = NB * GY;
+  uint32_t* cur = band_sm + (size_t)warp * (nL + GY + NB);
+  uint32_t* Rm = cur + nL;
+  uint32_t* Bm = Rm + GY;
+  for (int l = lane; l < nL; l += 32) cur[l] = WRITE ? lstart[l] + matA[(size_t)l * nchunks + chunk] : 0u;
   __syncwarp();
   const uint32_t lt = (1u << lane) - 1u;
   const int begin = chunk * per_warp, end = min(P, begin + per_warp);
@@ -81,84 +91,126 @@ __global__ void __launch_bounds__(kBandWarps * 32) band_rows_kernel(
     const uint32_t bmin = __reduce_min_sync(0xffffffffu, ne ? b0 : 0xffffu);
     const uint32_t bmax = __reduce_max_sync(0xffffffffu, ne ? b1 : 0u);
     for (uint32_t r = rmin; r < rmax; ++r) {
-      const bool in_row = ne && y0 <= r && r < y1;
-      for (uint32_t b = bmin; b <= bmax; ++b) {
-        const bool cov = in_row && b0 <= b && b <= b1;
-        const uint32_t m = __ballot_sync(0xffffffffu, cov);
-        if (m == 0) continue;
-        const uint32_t l = r * NB + b;
-        if (WRITE) {
-          const uint32_t base = cur[l];
-          if (cov) recs[base + __popc(m & lt)] = id;
-          __syncwarp();
-          if (lane == 0) cur[l] = base + __popc(m);
-        } else {
-          if (lane == 0) cur[l] += __popc(m);
+      const uint32_t m = __ballot_sync(0xffffffffu, ne && y0 <= r && r < y1);
+      if (lane == 0) Rm[r] = m;
+    }
+    for (uint32_t b = bmin; b <= bmax; ++b) {
+      const uint32_t m = __ballot_sync(0xffffffffu, ne && b0 <= b && b <= b1);
+      if (lane == 0) Bm[b] = m;
+    }
+    __syncwarp();
+    if (WRITE) {
+      if (ne) {
+        for (uint32_t r = y0; r < y1; ++r) {
+          const uint32_t rm = Rm[r];
+          for (uint32_t b = b0; b <= b1; ++b) recs[cur[r * NB + b] + __popc(rm & Bm[b] & lt)] = id;
         }
       }
+      __syncwarp();
+    }
+    const uint32_t nb = bmax - bmin + 1, ncell = (rmax - rmin) * nb;
+    for (uint32_t ci = lane; ci < ncell; ci += 32) {
+      const uint32_t r = rmin + ci / nb, b = bmin + ci % nb;
+      const uint32_t m = Rm[r] & Bm[b];
+      if (m) cur[r * NB + b] += __popc(m);
     }
     __syncwarp();
   }
   if (!WRITE) {
-    __syncwarp();
     for (int l = lane; l < nL; l += 32) matA[(size_t)l * nchunks + chunk] = cur[l];
   }
 }
 
-// ---- header: list starts, segment table (one CTA of 1024 threads, nL <= 1024) ---------------------
-__global__ void __launch_bounds__(1024) band_header_kernel(int nL, int nchunks, const uint32_t* __restrict__ matA,
-                                                            uint32_t* __restrict__ lstart, uint32_t* __restrict__ segbase,
-                                                            uint32_t* __restrict__ scan_len, uint32_t* __restrict__ tilemat) {
-  __shared__ uint32_t wsum[32];
-  const int l = threadIdx.x, lane = l & 31, warp = l >> 5;
-  uint32_t nseg = 0;
-  if (l < nL) {
-    const uint32_t a = matA[(size_t)l * nchunks], b = matA[(size_t)(l + 1) * nchunks];  // scanned, [nL*nchunks] = total
-    lstart[l] = a;
-    if (l == nL - 1) lstart[nL] = b;
-    nseg = (b - a + kBandSegRecs - 1) / kBandSegRecs;
-  }
-  const uint32_t inc = warp_incl_scan(nseg, lane);
-  if (lane == 31) wsum[warp] = inc;
+// Last-block-done ticket: returns true in every thread of the CTA that finishes last.
+__device__ __forceinline__ bool band_last_block(uint32_t* ticket) {
+  __shared__ uint32_t last;
+  __threadfence();
   __syncthreads();
-  if (warp == 0) {
-    const uint32_t w = wsum[lane];
-    const uint32_t wi = warp_incl_scan(w, lane);
-    wsum[lane] = wi - w;
-  }
+  if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1 ? 1u : 0u;
   __syncthreads();
-  const uint32_t ex = inc - nseg + wsum[warp];
-  if (l < nL) segbase[l] = ex;
-  if (l == nL - 1) {
-    const uint32_t S = ex + nseg;
-    segbase[nL] = S;
-    *scan_len = S * kBandTiles + 1;
-    tilemat[(size_t)S * kBandTiles] = 0;   // scanned into the grand total (== num_rendered)
+  if (last) __threadfence();
+  return last != 0u;
+}
+
+// ---- list scan + header -------------------------------------------------------------------------
+// One CTA per list: in-place exclusive scan of its chunk counts (matA row) and the list total.  The
+// CTA that finishes last turns the totals into list starts and the segment table.
+__global__ void __launch_bounds__(256) band_list_scan_kernel(int nL, int nchunks, uint32_t* __restrict__ matA,
+                                                             uint32_t* __restrict__ lcount, uint32_t* __restrict__ lstart,
+                                                             uint32_t* __restrict__ segbase, uint32_t* __restrict__ ticket) {
+  {
+    // CTA = list blockIdx.x; thread t owns entries [16 t, 16 t + 16) of the row (nchunks <= 4096, multiple of 8)
+    uint32_t* row = matA + (size_t)blockIdx.x * nchunks;
+    const int k0 = threadIdx.x * 16;
+    uint4 v[4];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      v[q] = make_uint4(0u, 0u, 0u, 0u);
+      if (k0 + 4 * q < nchunks) v[q] = *reinterpret_cast<const uint4*>(row + k0 + 4 * q);
+      sum += v[q].x + v[q].y + v[q].z + v[q].w;
+    }
+    uint32_t tot;
+    uint32_t run = block_excl_scan_256(sum, &tot);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint4 o;
+      o.x = run; run += v[q].x;
+      o.y = run; run += v[q].y;
+      o.z = run; run += v[q].z;
+      o.w = run; run += v[q].w;
+      if (k0 + 4 * q < nchunks) *reinterpret_cast<uint4*>(row + k0 + 4 * q) = o;
+    }
+    if (threadIdx.x == 0) lcount[blockIdx.x] = tot;
+  }
+  if (!band_last_block(ticket)) return;
+  // header: 256 threads, each owns a run of consecutive lists
+  const int per = (nL + 255) / 256;
+  const int lo = min(nL, (int)threadIdx.x * per), hi = min(nL, lo + per);
+  uint32_t recs_sum = 0, seg_sum = 0;
+  for (int q = lo; q < hi; ++q) {
+    const uint32_t c = __ldcg(lcount + q);
+    recs_sum += c;
+    seg_sum += (c + kBandSegRecs - 1) / kBandSegRecs;
+  }
+  uint32_t tot_r, tot_s;
+  uint32_t ex_r = block_excl_scan_256(recs_sum, &tot_r);
+  uint32_t ex_s = block_excl_scan_256(seg_sum, &tot_s);
+  for (int q = lo; q < hi; ++q) {
+    const uint32_t c = __ldcg(lcount + q);
+    lstart[q] = ex_r;
+    segbase[q] = ex_s;
+    ex_r += c;
+    ex_s += (c + kBandSegRecs - 1) / kBandSegRecs;
+  }
+  if (threadIdx.x == 0) {
+    lstart[nL] = tot_r;
+    segbase[nL] = tot_s;
   }
 }
 
 // Lane t appends the ids of the records (one per lane, coverage mask cm) that cover its tile, in lane
 // order, to its run of the stage starting at k; returns the advanced k.
 __device__ __forceinline__ uint32_t band_stage_group(uint32_t cm, uint32_t id, uint32_t lane_bit, int lane,
-                                                     uint32_t* stage, uint8_t* stage_tile, uint32_t k) {
+                                                     uint32_t* stage, uint32_t k) {
+  const uint32_t tag = (uint32_t)lane << kBandIdBits;
 #pragma unroll
   for (int jj = 0; jj < 32; ++jj) {
     const bool hit = (__shfl_sync(0xffffffffu, cm, jj) & lane_bit) != 0u;
-    const uint32_t idj = __shfl_sync(0xffffffffu, id, jj);
-    if (hit) {
-      stage[k] = idj;
-      stage_tile[k] = (uint8_t)lane;
-      ++k;
-    }
+    const uint32_t idj = __shfl_sync(0xffffffffu, id, jj) | tag;
+    if (hit) stage[k++] = idj;
   }
   return k;
 }
 
 // Flat flush: the stage is tile-major, so consecutive lanes write consecutive words of a run.
-__device__ __forceinline__ void band_flush(const uint32_t* stage, const uint8_t* stage_tile, const uint32_t* stage_delta,
-                                           uint32_t tot, int lane, uint32_t* __restrict__ out) {
+__device__ __forceinline__ void band_flush(const uint32_t* stage, const uint32_t* stage_delta, uint32_t tot, int lane,
+                                           uint32_t* __restrict__ out) {
   __syncwarp();
-  for (uint32_t q = lane; q < tot; q += 32) out[q + stage_delta[stage_tile[q]]] = stage[q];
+  for (uint32_t q = lane; q < tot; q += 32) {
+    const uint32_t v = stage[q];
+    out[q + stage_delta[v >> kBandIdBits]] = v & ((1u << kBandIdBits) - 1u);
+  }
   __syncwarp();
 }
 
@@ -168,15 +220,14 @@ template <bool WRITE>
 __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
     int nL, int NB, const uint32_t* __restrict__ lstart, const uint32_t* __restrict__ segbase,
     const uint32_t* __restrict__ recs, const uint2* __restrict__ rect, uint32_t* __restrict__ tilemat,
-    uint32_t* __restrict__ out) {
+    const uint32_t* __restrict__ tiletot, const uint32_t* __restrict__ tilestart, uint32_t* __restrict__ out) {
   extern __shared__ uint32_t band_sm[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   uint32_t* sb = band_sm;                                      // [nL + 1]
   const int sb_words = (nL + 1 + 31) & ~31;
-  // WRITE only: per warp [cap] ids, [32] run deltas, [cap] owning tile (bytes)
+  // WRITE only: per warp [cap] staged words, [32] run deltas
   uint32_t* stage = band_sm + sb_words + warp * kBandStageWords;
   uint32_t* stage_delta = stage + kBandStageCap;
-  uint8_t* stage_tile = reinterpret_cast<uint8_t*>(stage_delta + 32);
   for (int k = threadIdx.x; k <= nL; k += blockDim.x) sb[k] = segbase[k];
   __syncthreads();
   const uint32_t S = sb[nL];
@@ -195,8 +246,9 @@ __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
     uint32_t c = 0, goff = 0, start = 0, k = 0;
     bool staged = false;
     if (WRITE) {
-      goff = tilemat[e];
-      c = tilemat[e + 1] - goff;
+      const uint32_t within = tilemat[e];   // instances of this tile in earlier segments of the list
+      c = (s + 1 < nseg ? tilemat[e + 1] : tiletot[l * kBandTiles + lane]) - within;
+      goff = tilestart[l * kBandTiles + lane] + within;
       const uint32_t inc = warp_incl_scan(c, lane);
       start = inc - c;
       staged = __shfl_sync(0xffffffffu, inc, 31) <= (uint32_t)kBandStageCap;
@@ -216,16 +268,16 @@ __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
 #pragma unroll
         for (int jj = 0; jj < 32; ++jj) c += (__shfl_sync(0xffffffffu, cm, jj) & lane_bit) ? 1u : 0u;
       } else if (staged) {
-        k = band_stage_group(cm, id, lane_bit, lane, stage, stage_tile, k);
+        k = band_stage_group(cm, id, lane_bit, lane, stage, k);
       } else {
         // dense segment (> cap instances): stage and flush these 32 records on their own (<= 1024 instances)
         uint32_t cg = 0;
 #pragma unroll
         for (int jj = 0; jj < 32; ++jj) cg += (__shfl_sync(0xffffffffu, cm, jj) & lane_bit) ? 1u : 0u;
         const uint32_t inc = warp_incl_scan(cg, lane);
-        band_stage_group(cm, id, lane_bit, lane, stage, stage_tile, inc - cg);
+        band_stage_group(cm, id, lane_bit, lane, stage, inc - cg);
         stage_delta[lane] = goff + k - (inc - cg);   // k = instances of this tile already written
-        band_flush(stage, stage_tile, stage_delta, __shfl_sync(0xffffffffu, inc, 31), lane, out);
+        band_flush(stage, stage_delta, __shfl_sync(0xffffffffu, inc, 31), lane, out);
         k += cg;
       }
     }
@@ -233,33 +285,66 @@ __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
       tilemat[e] = c;
     } else if (staged) {
       stage_delta[lane] = goff - start;   // staged position -> output position, for this lane's tile
-      band_flush(stage, stage_tile, stage_delta, __shfl_sync(0xffffffffu, start + c, 31), lane, out);
+      band_flush(stage, stage_delta, __shfl_sync(0xffffffffu, start + c, 31), lane, out);
     }
   }
 }
 
-// ranges[tile] = [start, end) in the output list; (0, 0) for empty tiles like the reference's memset
-__global__ void __launch_bounds__(256) band_ranges_kernel(int T, int gx, int NB, const uint32_t* __restrict__ segbase,
-                                                           const uint32_t* __restrict__ tilemat, uint2* __restrict__ ranges) {
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t >= T) return;
-  const int r = t / gx, x = t - r * gx;
-  const int l = r * NB + x / kBandTiles, xl = x % kBandTiles;
-  const uint32_t sb = segbase[l], nseg = segbase[l + 1] - sb;
-  uint2 out = make_uint2(0u, 0u);
-  if (nseg) {
-    const size_t e = (size_t)sb * kBandTiles + (size_t)xl * nseg;
-    const uint32_t a = tilemat[e], b = tilemat[e + nseg];
-    if (b > a) out = make_uint2(a, b);
+// ---- tile scan + ranges -------------------------------------------------------------------------
+// One warp per tile slot (list l, lane x): in-place exclusive scan of its nseg_l segment counts and
+// the tile total.  The CTA that finishes last scans the totals into output positions and writes
+// ranges[tile] = [start, end), (0, 0) for empty tiles like the reference's memset
+// (identifyTileRanges, R3 rasterizer_impl.cu:116-138).
+__global__ void __launch_bounds__(256) band_tile_scan_kernel(int nL, int NB, int gx, int T,
+                                                             const uint32_t* __restrict__ segbase,
+                                                             uint32_t* __restrict__ tilemat, uint32_t* __restrict__ tiletot,
+                                                             uint32_t* __restrict__ tilestart, uint2* __restrict__ ranges,
+                                                             uint32_t* __restrict__ ticket) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int slots = nL * kBandTiles;
+  for (int slot = blockIdx.x * 8 + warp; slot < slots; slot += gridDim.x * 8) {
+    const int l = slot / kBandTiles, x = slot % kBandTiles;
+    const uint32_t sb = segbase[l], nseg = segbase[l + 1] - sb;
+    uint32_t* row = tilemat + (size_t)sb * kBandTiles + (size_t)x * nseg;
+    uint32_t carry = 0;
+    for (uint32_t k0 = 0; k0 < nseg; k0 += 128) {
+      uint32_t v[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t k = k0 + 32 * q + lane;
+        v[q] = k < nseg ? row[k] : 0u;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const uint32_t k = k0 + 32 * q + lane;
+        const uint32_t inc = warp_incl_scan(v[q], lane);
+        if (k < nseg) row[k] = carry + inc - v[q];
+        carry += __shfl_sync(0xffffffffu, inc, 31);
+      }
+    }
+    if (lane == 0) tiletot[slot] = carry;
   }
-  ranges[t] = out;
+  if (!band_last_block(ticket)) return;
+  const int per = (slots + 255) / 256;
+  const int lo = min(slots, (int)threadIdx.x * per), hi = min(slots, lo + per);
+  uint32_t sum = 0;
+  for (int q = lo; q < hi; ++q) sum += __ldcg(tiletot + q);
+  uint32_t tot;
+  uint32_t ex = block_excl_scan_256(sum, &tot);
+  for (int q = lo; q < hi; ++q) {
+    const uint32_t c = __ldcg(tiletot + q);
+    tilestart[q] = ex;
+    const int l = q / kBandTiles, x = (l % NB) * kBandTiles + q % kBandTiles;
+    if (x < gx) ranges[(l / NB) * gx + x] = c ? make_uint2(ex, ex + c) : make_uint2(0u, 0u);
+    ex += c;
+  }
 }
 
 inline cudaError_t band_bin(const BandWs& w, int P, int gx, int gy, int64_t R, const uint32_t* sorted_idx,
                             const uint2* srect, const uint2* rect, uint32_t* out, uint2* ranges, cudaStream_t st) {
   const int NB = band_count(gx), nL = NB * gy, nchunks = band_row_chunks(nL), T = gx * gy;
   const int per_warp = ((P + nchunks - 1) / nchunks + 31) & ~31;
-  const size_t smA = (size_t)kBandWarps * nL * sizeof(uint32_t);
+  const size_t smA = (size_t)kBandWarps * (nL + gy + NB) * sizeof(uint32_t);
   const int sb_words = (nL + 1 + 31) & ~31;
   const size_t smC = (size_t)sb_words * sizeof(uint32_t);
   const size_t smW = smC + (size_t)kBandWarps * kBandStageWords * sizeof(uint32_t);
@@ -267,35 +352,36 @@ inline cudaError_t band_bin(const BandWs& w, int P, int gx, int gy, int64_t R, c
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(band_expand_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(band_rows_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(band_rows_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    if (e != cudaSuccess) return e;
     attr_done = true;
   }
-  int sms = 148;
-  {
-    static int cached = 0;
-    if (!cached) {
-      int dev = 0;
-      cudaGetDevice(&dev);
-      cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
-    }
-    sms = cached > 0 ? cached : 148;
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
   }
-  const uint32_t nA = (uint32_t)((size_t)nL * nchunks);
-  cudaError_t e = cudaMemsetAsync(w.matA + nA, 0, sizeof(uint32_t), st);
+  cudaError_t e = cudaMemsetAsync(w.ticket, 0, 2 * sizeof(uint32_t), st);
   if (e != cudaSuccess) return e;
-  band_rows_kernel<false><<<nchunks / kBandWarps, kBandWarps * 32, smA, st>>>(P, per_warp, NB, nL, nchunks, sorted_idx,
-                                                                              srect, w.matA, nullptr);
-  e = exclusive_scan_u32(w.matA, nullptr, nA + 1, w.matA, w.mscan, nullptr, st);
-  if (e != cudaSuccess) return e;
-  band_header_kernel<<<1, 1024, 0, st>>>(nL, nchunks, w.matA, w.lstart, w.segbase, w.scan_len, w.tilemat);
-  band_rows_kernel<true><<<nchunks / kBandWarps, kBandWarps * 32, smA, st>>>(P, per_warp, NB, nL, nchunks, sorted_idx,
-                                                                             srect, w.matA, w.recs);
-  band_expand_kernel<false><<<sms * 8, kBandWarps * 32, smC, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect,
-                                                                    w.tilemat, nullptr);
-  e = exclusive_scan_u32_dyn(w.tilemat, (uint32_t)band_tilemat_bound(R, nL), w.scan_len, w.mscan, st);
-  if (e != cudaSuccess) return e;
-  band_ranges_kernel<<<(T + 255) / 256, 256, 0, st>>>(T, gx, NB, w.segbase, w.tilemat, ranges);
-  band_expand_kernel<true><<<sms * 2, kBandWarps * 32, smW, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect,
-                                                                   w.tilemat, out);
+  const int ctasA = nchunks / kBandWarps;
+  band_rows_kernel<false><<<ctasA, kBandWarps * 32, smA, st>>>(P, per_warp, NB, gy, nchunks, sorted_idx, srect, w.matA,
+                                                               nullptr, nullptr);
+  band_list_scan_kernel<<<nL, 256, 0, st>>>(nL, nchunks, w.matA, w.lcount, w.lstart, w.segbase, w.ticket);
+  band_rows_kernel<true><<<ctasA, kBandWarps * 32, smA, st>>>(P, per_warp, NB, gy, nchunks, sorted_idx, srect, w.matA,
+                                                              w.lstart, w.recs);
+  band_expand_kernel<false><<<sms * 8, kBandWarps * 32, smC, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect, w.tilemat,
+                                                                    nullptr, nullptr, nullptr);
+  const int slots = nL * kBandTiles;
+  const int ctasT = (slots + 7) / 8 < sms * 8 ? (slots + 7) / 8 : sms * 8;
+  band_tile_scan_kernel<<<ctasT, 256, 0, st>>>(nL, NB, gx, T, w.segbase, w.tilemat, w.tiletot, w.tilestart, ranges,
+                                               w.ticket + 1);
+  band_expand_kernel<true><<<sms * 3, kBandWarps * 32, smW, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect, w.tilemat,
+                                                                   w.tiletot, w.tilestart, out);
+  (void)R;
   return cudaGetLastError();
 }
 

@@ -142,15 +142,16 @@ inline size_t carve_binning(int64_t R, int W, int H, void* base, BinWs* ws) {
   const int T = gx * gy;
   if (band_path(gx, gy)) {
     const int nL = band_lists(gx, gy);
-    const size_t nA = (size_t)nL * band_row_chunks(nL) + 1, nB = band_tilemat_bound(R, nL);
     w.valA = c.take<uint32_t>(r);
     w.band.recs = c.take<uint32_t>(r);
-    w.band.matA = c.take<uint32_t>(nA);
+    w.band.matA = c.take<uint32_t>((size_t)nL * band_row_chunks(nL));
+    w.band.lcount = c.take<uint32_t>(nL);
     w.band.lstart = c.take<uint32_t>(nL + 1);
     w.band.segbase = c.take<uint32_t>(nL + 1);
-    w.band.scan_len = c.take<uint32_t>(4);
-    w.band.tilemat = c.take<uint32_t>(nB);
-    w.band.mscan = c.take<uint32_t>(scan_scratch_elems(nA > nB ? nA : nB) + 64);
+    w.band.tilemat = c.take<uint32_t>(band_tilemat_bound(R, nL));
+    w.band.tiletot = c.take<uint32_t>((size_t)nL * kBandTiles);
+    w.band.tilestart = c.take<uint32_t>((size_t)nL * kBandTiles);
+    w.band.ticket = c.take<uint32_t>(4);
   } else if (bin_fast_path(T)) {
     w.valA = c.take<uint32_t>(r);
     const size_t m = (size_t)T * bin_max_chunks(T) + 1;
