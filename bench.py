@@ -142,7 +142,7 @@ def make_scene(rank: int):
     return cam, sc, ct, target
 
 
-def algorithmic_bytes(P: int, R: int, W: int, H: int) -> dict:
+def algorithmic_bytes(P: int, R: int, W: int, H: int, Q: int = -1) -> dict:
     """Per-launch algorithmic HBM bytes of each phase."""
     WH = W * H
     T = ((W + 15) // 16) * ((H + 15) // 16)
@@ -150,9 +150,11 @@ def algorithmic_bytes(P: int, R: int, W: int, H: int) -> dict:
     return {
         "preprocess_fwd": 104 * P,                    # 44 B in + 60 B out per Gaussian
         "depth_sort": (4 * (4 + 8 + 8) + 4 + 16 + 12) * P,  # 4 LSD passes over (u32 key, u32 value) + rect gather + weight scan
-        # chunked counting sort: two walks over (id 4 B + rect 8 B) per Gaussian, one 4-B id
-        # write per instance, [tile][chunk] matrix written, scanned (r+w) and read back, ranges written
-        "binning": 2 * 12 * P + 4 * R + 16 * T * NC + 8 * T,
+        # band binning, Q band records: stage A walks (rect 8 B [+ id 4 B]) per Gaussian twice
+        # and writes 4 B per record; stage B reads each record (4 B + 4 B of its rect) twice and writes one
+        # 4-B id per instance; count matrices (r+w) and ranges.  One-level fallback when Q < 0.
+        "binning": (2 * 8 * P + 4 * P + 4 * Q + 2 * 8 * Q + 4 * R + 3 * 4 * (Q // 4) + 8 * T) if Q >= 0
+                   else 2 * 12 * P + 4 * R + 16 * T * NC + 8 * T,
         # blend kernels: HBM sees the id list once, each record once (re-reads by other tiles hit L2) and the
         # images; the per-instance record / gradient traffic (L2_BYTES below) is L2 and shared-memory work
         "render_fwd": 4 * R + 48 * P + 28 * WH,
@@ -167,6 +169,9 @@ def l2_bytes(P: int, R: int) -> dict:
     return {"render_fwd": 52 * R, "render_bwd": 52 * R + 48 * R}
 
 
+BAND_LISTS: dict = {}   # {"n": (row, band) lists of the benchmarked tile grid}
+
+
 def launches_per_step(T: int, P: int) -> int:
     """Kernel launches of one fwd+bwd (radix pass = hist + 3 scan + scatter)."""
     scan = 3
@@ -175,7 +180,9 @@ def launches_per_step(T: int, P: int) -> int:
         pre = 1 + 1
     else:
         pre = 1 + 4 * rp + 1 + scan      # preprocess, depth argsort, rect gather, weight scan
-    if T <= 12288:                       # counting-sort binning: count walk, matrix scan, ranges, scatter walk
+    if BAND_LISTS.get("n", 1 << 30) <= 1024:
+        binning = 6                      # band binning: rows x2, list scan, expand x2, tile scan
+    elif T <= 12288:                     # one-level counting sort: count walk, matrix scan, ranges, scatter walk
         binning = 1 + scan + 1 + 1
     else:                                # radix fallback: emit, 2 tile passes, ranges
         binning = 1 + 2 * rp + 1
@@ -196,6 +203,8 @@ def run_ours(args, rank, world, local):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     grads_flat = torch.zeros(P * 14, device=dev)
 
+    last_binning: list = []
+
     def step_resident(exchange: bool = True):
         R, color, radii, geom, binning, img, depth, opac, n_touched = RC.rasterize_gaussians(
             bg, sc["means3D"], sc["colors_precomp"], sc["opacities"], sc["scales"], sc["rotations"], 1.0, e, view, full,
@@ -203,6 +212,7 @@ def run_ours(args, rank, world, local):
         out = RC.rasterize_gaussians_backward(bg, sc["means3D"], radii, sc["colors_precomp"], sc["scales"],
                                               sc["rotations"], 1.0, e, view, full, proj, cam.tanfovx, cam.tanfovy,
                                               ct["color"], ct["depth"], e, 0, center, geom, R, binning, img, False)
+        last_binning[:] = [binning]
         if world > 1 and exchange:
             # training exchange step: sum the Gaussian-parameter gradients over the view shards
             torch.cat([out[3].flatten(), out[1].flatten(), out[2].flatten(), out[6].flatten(), out[7].flatten()],
@@ -333,7 +343,9 @@ def run_ours(args, rank, world, local):
     if rank != 0:
         return None
     phase_ms = {k: sum(v) / len(v) for k, v in phases.items()}
-    ab = algorithmic_bytes(P, R, W, H)
+    Q = int(L.lib().pg_raster_band_records(W, H, int(R), last_binning[0].data_ptr(), None)) if last_binning else -1
+    BAND_LISTS["n"] = ((W + 15) // 16 + 31) // 32 * ((H + 15) // 16)
+    ab = algorithmic_bytes(P, R, W, H, Q)
     pk = peaks()
     dom = max(phase_ms, key=phase_ms.get)
     achieved = ab[dom] / (phase_ms[dom] * 1e-3) / 1e9
@@ -351,7 +363,7 @@ def run_ours(args, rank, world, local):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "C2: 3DGS rasterizer fwd+bwd with pose grads, 500k synthetic Gaussians, one 1226x370 view "
                                "per GPU per step (BASELINE.json configs[1])",
-                   "P": P, "W": W, "H": H, "num_rendered": int(R), "views_per_step": world,
+                   "P": P, "W": W, "H": H, "num_rendered": int(R), "band_records": Q, "views_per_step": world,
                    "l2": "flushed between steps (256 MiB write)",
                    "exchange": "NCCL all-reduce of Gaussian-parameter grads (28 MB)" if world > 1 else "none (N=1)"},
         "clocks": clocks,
@@ -369,7 +381,10 @@ def run_ours(args, rank, world, local):
 
 
 # per-launch dram bytes of the dominant kernels from profiles/ (ncu --set full), filled in as captured
-TRAFFIC: dict = {}
+# (profiles/r01_ncu_full_top_kernels_v4.csv: dram__bytes_read.sum + dram__bytes_write.sum, summed over the
+# kernels of a phase; the capture runs the step without the L2 flush, so inputs produced by the previous
+# kernel are L2 hits)
+TRAFFIC: dict = {"depth_sort": 8.03e6, "binning": 81.7e6, "render_fwd": 3.41e6, "render_bwd": 13.05e6}
 
 
 def cpu_baseline_line(args) -> dict | None:

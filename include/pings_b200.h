@@ -151,6 +151,11 @@ int pg_raster_debug_views(int variant, int P, int width, int height, int64_t num
                           const float** final_T, const uint32_t** n_contrib,
                           const float** records /* float4[3P] */, const uint32_t** depth_sorted_idx);
 
+/* Measurement accessor: number of (Gaussian, tile row, 32-tile band) records the band binning of the
+ * last stage 2 on this workspace produced (synchronises `stream`); -1 when the tile grid used another
+ * binning path.  Used by bench.py for the algorithmic byte count; no reference counterpart. */
+int64_t pg_raster_band_records(int width, int height, int64_t num_rendered, void* binning_ws, void* stream);
+
 
 /* ------------------------------------------------------------------------------------------
  * Neural-point map: voxel-hash kNN, top-k + inverse-distance interpolation, decoder MLP

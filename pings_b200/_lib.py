@@ -120,6 +120,8 @@ def lib() -> C.CDLL:
                                      C.POINTER(PgRasterBwdIn), C.POINTER(PgRasterBwdOut), fp]
     L.pg_raster_debug_views.restype = C.c_int
     L.pg_raster_debug_views.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, fp, fp, fp] + [C.POINTER(fp)] * 6
+    L.pg_raster_band_records.restype = C.c_int64
+    L.pg_raster_band_records.argtypes = [C.c_int, C.c_int, C.c_int64, fp, fp]
     L.pg_np_radius_search.restype = C.c_int
     L.pg_np_radius_search.argtypes = [C.POINTER(PgNeuralMap), C.c_int64, fp, C.c_int, fp, fp, fp]
     L.pg_np_query_feature.restype = C.c_int

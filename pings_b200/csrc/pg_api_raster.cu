@@ -250,4 +250,17 @@ int pg_raster_debug_views(int variant, int P, int width, int height, int64_t num
   return PG_OK;
 }
 
+int64_t pg_raster_band_records(int width, int height, int64_t num_rendered, void* binning_ws, void* stream) {
+  const int gx = div_up(width, kTile), gy = div_up(height, kTile);
+  if (!binning_ws || num_rendered <= 0 || !band_path(gx, gy)) return -1;
+  BinWs bw;
+  carve_binning(num_rendered, width, height, binning_ws, &bw);
+  uint32_t q = 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (cudaMemcpyAsync(&q, bw.band.lstart + band_lists(gx, gy), sizeof(q), cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+      cudaStreamSynchronize(st) != cudaSuccess)
+    return -1;
+  return (int64_t)q;
+}
+
 }  // extern "C"
