@@ -246,6 +246,14 @@ typedef struct PgMlp {
 /* y[N,out_dim] = mlp(x[N,in_dim]).  hidden_save (optional) receives the post-activation hidden
  * states [hidden_level][N,hidden_dim] needed by the backward. */
 int pg_mlp_forward(const PgMlp* mlp, int64_t N, const float* x, float* y, float* hidden_save, void* stream);
+/* Same with an explicit kernel choice.  PG_MLP_TCGEN05: tcgen05/TMEM kernel with 3xTF32 split
+ * accumulation (fp32-level accuracy; in_dim, hidden_dim <= 128, out_dim <= 64), which PG_MLP_AUTO
+ * picks for batches of >= 4096 rows (Decoder.mlp_batch, DEC:84-98); PG_MLP_SIMT: fp32 FMA kernel. */
+#define PG_MLP_AUTO 0
+#define PG_MLP_SIMT 1
+#define PG_MLP_TCGEN05 2
+int pg_mlp_forward_impl(const PgMlp* mlp, int64_t N, const float* x, float* y, float* hidden_save, int impl,
+                        void* stream);
 /* dX (optional) overwritten; dW[l], dB[l] ACCUMULATED into (caller zero-fills); dB[l] may be NULL. */
 int pg_mlp_backward(const PgMlp* mlp, int64_t N, const float* x, const float* hidden_save, const float* dY,
                     float* dX, float* const* dW, float* const* dB, void* stream);

@@ -133,6 +133,8 @@ def lib() -> C.CDLL:
     L.pg_np_query_feature_backward.argtypes = [C.POINTER(PgQueryArgs), C.c_int64] + [fp] * 12
     L.pg_mlp_forward.restype = C.c_int
     L.pg_mlp_forward.argtypes = [C.POINTER(PgMlp), C.c_int64, fp, fp, fp, fp]
+    L.pg_mlp_forward_impl.restype = C.c_int
+    L.pg_mlp_forward_impl.argtypes = [C.POINTER(PgMlp), C.c_int64, fp, fp, fp, C.c_int, fp]
     L.pg_mlp_backward.restype = C.c_int
     L.pg_mlp_backward.argtypes = [C.POINTER(PgMlp), C.c_int64, fp, fp, fp, fp, C.POINTER(fp), C.POINTER(fp), fp]
     L.pg_sdf_query.restype = C.c_int

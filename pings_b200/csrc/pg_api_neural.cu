@@ -1,5 +1,6 @@
 // C-ABI entry points of the neural-point path (see include/pings_b200.h).
 #include "pg_sdf.cuh"
+#include "pg_mlp_tc.cuh"
 
 using namespace pg;
 
@@ -74,6 +75,7 @@ MlpDev to_dev(const PgMlp* m) {
 }
 
 constexpr size_t kMaxDynSmem = 227 * 1024;
+constexpr int64_t kTcAutoMinRows = 4096;
 
 template <typename F>
 int with_cpl(int K, F&& f) {
@@ -158,12 +160,22 @@ int pg_np_query_feature_backward(const PgQueryArgs* args, int64_t N, const float
   return PG_OK;
 }
 
-int pg_mlp_forward(const PgMlp* mlp, int64_t N, const float* x, float* y, float* hidden_save, void* stream) {
-  if (N < 0 || !mlp_ok(mlp)) return PG_ERR_ARG;
+int pg_mlp_forward_impl(const PgMlp* mlp, int64_t N, const float* x, float* y, float* hidden_save, int impl,
+                        void* stream) {
+  if (N < 0 || !mlp_ok(mlp) || impl < PG_MLP_AUTO || impl > PG_MLP_TCGEN05) return PG_ERR_ARG;
   if (N == 0) return PG_OK;
   if (!x || !y) return PG_ERR_ARG;
   cudaStream_t st = (cudaStream_t)stream;
   const MlpDev m = to_dev(mlp);
+  const bool tc_ok = tc_supported(m);
+  if (impl == PG_MLP_TCGEN05 && !tc_ok) return PG_ERR_UNSUPPORTED;
+  // large batches (mlp_batch, spawn_gaussians) go to the tensor cores; small ones are latency bound
+  if (impl == PG_MLP_TCGEN05 || (impl == PG_MLP_AUTO && tc_ok && N >= kTcAutoMinRows)) {
+    Phase ph("mlp_forward_tc", st);
+    PG_CUDA(mlp_tc_forward(m, N, x, y, hidden_save, st));
+    PG_LAUNCH_CHECK(0, st);
+    return PG_OK;
+  }
   const size_t smem = mlp_smem_floats(m) * sizeof(float);
   if (smem > kMaxDynSmem) return PG_ERR_UNSUPPORTED;
   PG_CUDA(cudaFuncSetAttribute(mlp_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -171,6 +183,10 @@ int pg_mlp_forward(const PgMlp* mlp, int64_t N, const float* x, float* y, float*
   mlp_forward_kernel<<<(unsigned)((N + kMlpRows - 1) / kMlpRows), kMlpThreads, smem, st>>>(m, N, x, y, hidden_save);
   PG_LAUNCH_CHECK(0, st);
   return PG_OK;
+}
+
+int pg_mlp_forward(const PgMlp* mlp, int64_t N, const float* x, float* y, float* hidden_save, void* stream) {
+  return pg_mlp_forward_impl(mlp, N, x, y, hidden_save, PG_MLP_AUTO, stream);
 }
 
 int pg_mlp_backward(const PgMlp* mlp, int64_t N, const float* x, const float* hidden_save, const float* dY,

@@ -1,0 +1,259 @@
+// Decoder MLP on the 5th-gen tensor cores (tcgen05 + TMEM), for the large-batch `mlp_batch` calls
+// (DEC = model/decoder.py:84-98; spawn_gaussians runs 5 of them per neural point, GR:609-714).
+//
+// One CTA (128 threads) owns a 128-row tile and runs the whole layer chain on it:
+//   * operands live in shared memory in the no-swizzle K-major canonical layout
+//     [K/4 chunks][rows][4 floats] (a core matrix = 8 rows x 16 B contiguous; SBO = 128 B between
+//     row groups, LBO = rows*16 B between the two 16-B K chunks of one K=8 MMA step);
+//   * fp32 accuracy comes from the 3xTF32 split: every operand is stored as hi (low 13 mantissa
+//     bits cleared, exactly what kind::tf32 reads) and lo = v - hi, and each K step issues
+//     hi*hi + lo*hi + hi*lo into the same fp32 TMEM accumulator (lo*lo < 2^-22 relative is dropped);
+//   * one elected thread issues tcgen05.mma (M=128, N = piece of <= 64 output units, K=8 per
+//     instruction) and commits to an mbarrier; weights are streamed per layer in 64-unit pieces so
+//     hidden = 128 fits (2 x 64 KB activations + 2 x 32 KB weights);
+//   * epilogue: thread t reads accumulator row t with tcgen05.ld (32x32b: lane = row), adds the
+//     bias, applies ReLU/LeakyReLU and writes the next layer's hi/lo operands straight back in the
+//     canonical layout (consecutive threads -> consecutive 16 B: conflict free), so activations never
+//     leave the SM between layers.
+#pragma once
+#include "pg_mlp.cuh"
+
+namespace pg {
+
+constexpr int kTcRows = 128;
+constexpr int kTcThreads = 128;
+constexpr int kTcPiece = 64;     // output units per weight piece / MMA N
+constexpr int kTcMaxDim = 128;   // in_dim, hidden <= 128
+
+__host__ __device__ inline int tc_round8(int v) { return (v + 7) & ~7; }
+__host__ __device__ inline int tc_round16(int v) { return (v + 15) & ~15; }
+__host__ __device__ inline int tc_kmax(const MlpDev& m) {
+  const int a = tc_round8(m.in_dim), b = tc_round16(m.hidden);   // the epilogue writes 16 columns at a time
+  return a > b ? a : b;
+}
+__host__ __device__ inline int tc_tmem_cols(const MlpDev& m) {
+  int need = tc_round16(m.hidden);
+  const int o = tc_round16(m.out_dim);
+  if (o > need) need = o;
+  int c = 32;
+  while (c < need) c <<= 1;
+  return c;
+}
+// bytes: A hi/lo [Kmax/4][128][16 B] x2, W hi/lo [Kmax/4][64][16 B] x2, mbarrier + tmem slot
+__host__ __device__ inline size_t tc_smem_bytes(const MlpDev& m) {
+  const size_t k = (size_t)tc_kmax(m);
+  return 2 * k * kTcRows * 4 + 2 * k * kTcPiece * 4 + 64;
+}
+inline bool tc_supported(const MlpDev& m) {
+  return m.in_dim <= kTcMaxDim && m.hidden <= kTcMaxDim && m.out_dim <= kTcPiece && tc_smem_bytes(m) <= 227 * 1024;
+}
+
+__device__ __forceinline__ uint32_t tc_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// K-major, SWIZZLE_NONE shared-memory matrix descriptor (sm_100 version field = 1).
+__device__ __forceinline__ uint64_t tc_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3fffu);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fffu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fffu) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+// kind::tf32, fp32 accumulate, A and B K-major, M = 128
+__device__ __forceinline__ uint32_t tc_idesc(int n) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kTcRows >> 4) << 24);
+}
+__device__ __forceinline__ void tc_mma(uint32_t tmem_d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "l"(a), "l"(b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t mbar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(mbar) : "memory");
+}
+__device__ __forceinline__ void tc_mbar_wait(uint32_t mbar, uint32_t parity) {
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+        : "=r"(ok)
+        : "r"(mbar), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, "
+      "[%16];\n"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tc_split(float v, float& hi, float& lo) {
+  hi = __uint_as_float(__float_as_uint(v) & 0xffffe000u);
+  lo = v - hi;
+}
+
+template <int COLS>
+__global__ void __launch_bounds__(kTcThreads) mlp_tc_forward_kernel(MlpDev m, long long N, const float* __restrict__ x,
+                                                                    float* __restrict__ y, float* __restrict__ hsave) {
+  extern __shared__ __align__(128) unsigned char tc_sm[];
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int kmax = tc_kmax(m);
+  float* A_hi = reinterpret_cast<float*>(tc_sm);
+  float* A_lo = A_hi + (size_t)kmax * kTcRows;
+  float* W_hi = A_lo + (size_t)kmax * kTcRows;
+  float* W_lo = W_hi + (size_t)kmax * kTcPiece;
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(W_lo + (size_t)kmax * kTcPiece);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 1);
+
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem_u32(tmem_slot)),
+                 "n"(COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tc_smem_u32(mbar)) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t mbar_a = tc_smem_u32(mbar);
+
+  // stage the input tile: thread t = row t
+  const long long row = (long long)blockIdx.x * kTcRows + tid;
+  {
+    const int kp = tc_round8(m.in_dim);
+    const float* xr = x + row * m.in_dim;
+    for (int k0 = 0; k0 < kp; k0 += 4) {
+      float4 h, l;
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = (row < N && k0 + j < m.in_dim) ? xr[k0 + j] : 0.f;
+      tc_split(v[0], h.x, l.x); tc_split(v[1], h.y, l.y); tc_split(v[2], h.z, l.z); tc_split(v[3], h.w, l.w);
+      const size_t o = ((size_t)(k0 >> 2) * kTcRows + tid) * 4;
+      *reinterpret_cast<float4*>(A_hi + o) = h;
+      *reinterpret_cast<float4*>(A_lo + o) = l;
+    }
+  }
+  uint32_t phase = 0;
+  for (int l = 0; l <= m.levels; ++l) {
+    const int Din = mlp_layer_in(m, l), Dout = mlp_layer_out(m, l);
+    const int kp = tc_round8(Din);
+    const float* Wg = m.W[l];
+    for (int n0 = 0; n0 < Dout; n0 += kTcPiece) {
+      const int np = min(kTcPiece, Dout - n0), NP = tc_round16(np);
+      // weight piece -> [kp/4][NP][4] hi / lo   (W is [Dout][Din] row-major = K-major already)
+      for (int i = tid; i < NP * (kp >> 2); i += kTcThreads) {
+        const int n = i % NP, kc = i / NP;
+        float4 h, lo4;
+        float v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int k = kc * 4 + j;
+          v[j] = (n < np && k < Din) ? __ldg(Wg + (size_t)(n0 + n) * Din + k) : 0.f;
+        }
+        tc_split(v[0], h.x, lo4.x); tc_split(v[1], h.y, lo4.y); tc_split(v[2], h.z, lo4.z); tc_split(v[3], h.w, lo4.w);
+        const size_t o = ((size_t)kc * NP + n) * 4;
+        *reinterpret_cast<float4*>(W_hi + o) = h;
+        *reinterpret_cast<float4*>(W_lo + o) = lo4;
+      }
+      // generic-proxy shared writes (A from the previous epilogue, W) -> visible to the tensor core
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncthreads();
+      if (tid == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t idesc = tc_idesc(NP);
+        const uint32_t a_hi = tc_smem_u32(A_hi), a_lo = tc_smem_u32(A_lo);
+        const uint32_t w_hi = tc_smem_u32(W_hi), w_lo = tc_smem_u32(W_lo);
+        const uint32_t a_lbo = kTcRows * 16, w_lbo = (uint32_t)NP * 16;
+        for (int ks = 0; ks < (kp >> 3); ++ks) {
+          const uint32_t ao = (uint32_t)ks * 2u * a_lbo, wo = (uint32_t)ks * 2u * w_lbo;
+          const uint64_t dah = tc_desc(a_hi + ao, a_lbo, 128), dal = tc_desc(a_lo + ao, a_lbo, 128);
+          const uint64_t dwh = tc_desc(w_hi + wo, w_lbo, 128), dwl = tc_desc(w_lo + wo, w_lbo, 128);
+          tc_mma(tmem + (uint32_t)n0, dah, dwh, idesc, ks > 0 ? 1u : 0u);
+          tc_mma(tmem + (uint32_t)n0, dal, dwh, idesc, 1u);
+          tc_mma(tmem + (uint32_t)n0, dah, dwl, idesc, 1u);
+        }
+        tc_commit(mbar_a);
+      }
+      tc_mbar_wait(mbar_a, phase);
+      phase ^= 1u;
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
+    // epilogue: thread t <- accumulator row t (TMEM lane 32*warp + lane)
+    const bool last = l == m.levels;
+    const float* Bg = m.B[l];
+    const int cols = tc_round16(Dout);
+    float* hs = (!last && hsave) ? hsave + (size_t)l * N * m.hidden : nullptr;
+    for (int c0 = 0; c0 < cols; c0 += 16) {
+      uint32_t r[16];
+      tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, r);
+      float v[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int c = c0 + j;
+        float t = __uint_as_float(r[j]);
+        if (c < Dout) {
+          if (Bg) t += __ldg(Bg + c);
+          if (!last) t = mlp_act(t, m.leaky);
+        } else {
+          t = 0.f;
+        }
+        v[j] = t;
+      }
+      if (last) {
+        if (row < N) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (c0 + j < Dout) y[row * m.out_dim + c0 + j] = v[j];
+        }
+      } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          float4 h, lo4;
+          tc_split(v[4 * q + 0], h.x, lo4.x); tc_split(v[4 * q + 1], h.y, lo4.y);
+          tc_split(v[4 * q + 2], h.z, lo4.z); tc_split(v[4 * q + 3], h.w, lo4.w);
+          const size_t o = ((size_t)((c0 >> 2) + q) * kTcRows + tid) * 4;
+          *reinterpret_cast<float4*>(A_hi + o) = h;
+          *reinterpret_cast<float4*>(A_lo + o) = lo4;
+        }
+        if (hs && row < N) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (c0 + j < Dout) hs[row * Dout + c0 + j] = v[j];
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(COLS) : "memory");
+  }
+}
+
+inline cudaError_t mlp_tc_forward(const MlpDev& m, long long N, const float* x, float* y, float* hsave, cudaStream_t st) {
+  const size_t smem = tc_smem_bytes(m);
+  const unsigned grid = (unsigned)((N + kTcRows - 1) / kTcRows);
+  const int cols = tc_tmem_cols(m);
+  cudaError_t e;
+#define PG_TC_LAUNCH(C)                                                                                          \
+  e = cudaFuncSetAttribute(mlp_tc_forward_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);    \
+  if (e != cudaSuccess) return e;                                                                                \
+  mlp_tc_forward_kernel<C><<<grid, kTcThreads, smem, st>>>(m, N, x, y, hsave);
+  if (cols <= 32) { PG_TC_LAUNCH(32) }
+  else if (cols <= 64) { PG_TC_LAUNCH(64) }
+  else { PG_TC_LAUNCH(128) }
+#undef PG_TC_LAUNCH
+  return cudaGetLastError();
+}
+
+}  // namespace pg

@@ -60,6 +60,25 @@ class _MlpFn(torch.autograd.Function):
         return (None, None if dX is None else dX.reshape(*ctx.lead, x2.shape[1]), *grads)
 
 
+MLP_AUTO, MLP_SIMT, MLP_TCGEN05 = 0, 1, 2
+
+
+def mlp_forward_impl(dec, x, impl: int = MLP_AUTO, save_hidden: bool = False):
+    """Forward only, with an explicit kernel choice (pg_mlp_forward_impl): returns (y, hidden|None)."""
+    lib = L.lib()
+    if not x.is_cuda:
+        raise RuntimeError("pings_b200.Decoder: expected CUDA tensors (there is no CPU fallback)")
+    x2 = x.detach().reshape(-1, x.shape[-1]).to(torch.float32).contiguous()
+    N, dev = x2.shape[0], x2.device
+    mlp, keep = dec._mlp_struct()
+    y = torch.empty(N, dec.mlp_out_dim, dtype=torch.float32, device=dev)
+    hs = torch.empty(dec.hidden_level, N, dec.hidden_dim, dtype=torch.float32, device=dev) if save_hidden else None
+    with torch.cuda.device(dev):
+        L.check(lib.pg_mlp_forward_impl(C.byref(mlp), N, x2.data_ptr(), y.data_ptr(), L.ptr(hs), impl,
+                                        torch.cuda.current_stream(dev).cuda_stream), "mlp forward")
+    return y, hs
+
+
 class Decoder(nn.Module):
     def __init__(self, config, input_feature_dim, hidden_dim, hidden_level, out_dim, out_k=1, pos_dim=3,
                  is_time_conditioned=False):
