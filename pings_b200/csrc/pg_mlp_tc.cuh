@@ -42,7 +42,7 @@ __host__ __device__ inline int tc_tmem_cols(const MlpDev& m) {
 // bytes: A hi/lo [Kmax/4][128][16 B] x2, W hi/lo [Kmax/4][64][16 B] x2, mbarrier + tmem slot
 __host__ __device__ inline size_t tc_smem_bytes(const MlpDev& m) {
   const size_t k = (size_t)tc_kmax(m);
-  return 2 * k * kTcRows * 4 + 2 * k * kTcPiece * 4 + 64;
+  return 2 * k * kTcRows * 4 + 2 * k * kTcPiece * 4 + (size_t)PG_MLP_MAX_LAYERS * kTcMaxDim * 4 + 64;
 }
 inline bool tc_supported(const MlpDev& m) {
   return m.in_dim <= kTcMaxDim && m.hidden <= kTcMaxDim && m.out_dim <= kTcPiece && tc_smem_bytes(m) <= 227 * 1024;
@@ -107,7 +107,8 @@ __global__ void __launch_bounds__(kTcThreads) mlp_tc_forward_kernel(MlpDev m, lo
   float* A_lo = A_hi + (size_t)kmax * kTcRows;
   float* W_hi = A_lo + (size_t)kmax * kTcRows;
   float* W_lo = W_hi + (size_t)kmax * kTcPiece;
-  uint64_t* mbar = reinterpret_cast<uint64_t*>(W_lo + (size_t)kmax * kTcPiece);
+  float* bias_s = W_lo + (size_t)kmax * kTcPiece;   // [layer][128], zero padded (also when the layer has no bias)
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(bias_s + PG_MLP_MAX_LAYERS * kTcMaxDim);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 1);
 
   if (warp == 0) {
@@ -115,6 +116,10 @@ __global__ void __launch_bounds__(kTcThreads) mlp_tc_forward_kernel(MlpDev m, lo
                  "n"(COLS)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  for (int i = tid; i < (m.levels + 1) * kTcMaxDim; i += kTcThreads) {
+    const int l = i / kTcMaxDim, c = i % kTcMaxDim;
+    bias_s[i] = (m.B[l] && c < mlp_layer_out(m, l)) ? __ldg(m.B[l] + c) : 0.f;
   }
   if (tid == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tc_smem_u32(mbar)) : "memory");
@@ -126,20 +131,40 @@ __global__ void __launch_bounds__(kTcThreads) mlp_tc_forward_kernel(MlpDev m, lo
   const uint32_t tmem = *tmem_slot;
   const uint32_t mbar_a = tc_smem_u32(mbar);
 
-  // stage the input tile: thread t = row t
-  const long long row = (long long)blockIdx.x * kTcRows + tid;
+  // stage the input tile: the tile's rows are one contiguous block of x, read fully coalesced
+  const long long row0 = (long long)blockIdx.x * kTcRows;
+  const long long row = row0 + tid;
   {
-    const int kp = tc_round8(m.in_dim);
-    const float* xr = x + row * m.in_dim;
-    for (int k0 = 0; k0 < kp; k0 += 4) {
-      float4 h, l;
-      float v[4];
+    const int Din = m.in_dim, kp = tc_round8(Din);
+    const int total = kTcRows * Din;
+    const long long left = (N - row0) * Din;
+    const int valid = left < total ? (int)left : total;
+    const float* xb = x + row0 * Din;
+    const float inv_din = 1.0f / (float)Din;   // (i + 0.5) * inv floors exactly for i < 2^14, Din <= 128
+    for (int i0 = 0; i0 < total; i0 += kTcThreads * 8) {
+      float v[8];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) v[j] = (row < N && k0 + j < m.in_dim) ? xr[k0 + j] : 0.f;
-      tc_split(v[0], h.x, l.x); tc_split(v[1], h.y, l.y); tc_split(v[2], h.z, l.z); tc_split(v[3], h.w, l.w);
-      const size_t o = ((size_t)(k0 >> 2) * kTcRows + tid) * 4;
-      *reinterpret_cast<float4*>(A_hi + o) = h;
-      *reinterpret_cast<float4*>(A_lo + o) = l;
+      for (int j = 0; j < 8; ++j) {
+        const int i = i0 + j * kTcThreads + tid;
+        v[j] = i < valid ? __ldg(xb + i) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int i = i0 + j * kTcThreads + tid;
+        if (i < total) {
+          const int r = (int)(((float)i + 0.5f) * inv_din), k = i - r * Din;
+          float h, lo;
+          tc_split(v[j], h, lo);
+          const size_t o = ((size_t)(k >> 2) * kTcRows + r) * 4 + (k & 3);
+          A_hi[o] = h;
+          A_lo[o] = lo;
+        }
+      }
+    }
+    for (int k = Din; k < kp; ++k) {   // K padding of the first layer
+      const size_t o = ((size_t)(k >> 2) * kTcRows + tid) * 4 + (k & 3);
+      A_hi[o] = 0.f;
+      A_lo[o] = 0.f;
     }
   }
   uint32_t phase = 0;
@@ -149,20 +174,45 @@ __global__ void __launch_bounds__(kTcThreads) mlp_tc_forward_kernel(MlpDev m, lo
     const float* Wg = m.W[l];
     for (int n0 = 0; n0 < Dout; n0 += kTcPiece) {
       const int np = min(kTcPiece, Dout - n0), NP = tc_round16(np);
-      // weight piece -> [kp/4][NP][4] hi / lo   (W is [Dout][Din] row-major = K-major already)
-      for (int i = tid; i < NP * (kp >> 2); i += kTcThreads) {
-        const int n = i % NP, kc = i / NP;
-        float4 h, lo4;
-        float v[4];
+      // weight piece -> [kp/4][NP][4] hi / lo   (W is [Dout][Din] row-major = K-major already);
+      // loads are issued four chunks at a time so their latencies overlap
+      const int chunks = NP * (kp >> 2);
+      const float inv_np = 1.0f / (float)NP;
+      const bool vec = (Din & 3) == 0 && (reinterpret_cast<uintptr_t>(Wg) & 15) == 0;
+      for (int i0 = 0; i0 < chunks; i0 += kTcThreads * 4) {
+        float4 v[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const int k = kc * 4 + j;
-          v[j] = (n < np && k < Din) ? __ldg(Wg + (size_t)(n0 + n) * Din + k) : 0.f;
+        for (int q = 0; q < 4; ++q) {
+          const int i = i0 + q * kTcThreads + tid;
+          v[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (i < chunks) {
+            const int kc = (int)(((float)i + 0.5f) * inv_np), n = i - kc * NP;
+            if (n < np) {
+              const float* wr = Wg + (size_t)(n0 + n) * Din + kc * 4;
+              if (vec) {
+                if (kc * 4 < Din) v[q] = __ldg(reinterpret_cast<const float4*>(wr));
+              } else {
+                if (kc * 4 + 0 < Din) v[q].x = __ldg(wr + 0);
+                if (kc * 4 + 1 < Din) v[q].y = __ldg(wr + 1);
+                if (kc * 4 + 2 < Din) v[q].z = __ldg(wr + 2);
+                if (kc * 4 + 3 < Din) v[q].w = __ldg(wr + 3);
+              }
+            }
+          }
         }
-        tc_split(v[0], h.x, lo4.x); tc_split(v[1], h.y, lo4.y); tc_split(v[2], h.z, lo4.z); tc_split(v[3], h.w, lo4.w);
-        const size_t o = ((size_t)kc * NP + n) * 4;
-        *reinterpret_cast<float4*>(W_hi + o) = h;
-        *reinterpret_cast<float4*>(W_lo + o) = lo4;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int i = i0 + q * kTcThreads + tid;
+          if (i < chunks) {
+            const int kc = (int)(((float)i + 0.5f) * inv_np), n = i - kc * NP;
+            float4 h, lo4;
+            tc_split(v[q].x, h.x, lo4.x); tc_split(v[q].y, h.y, lo4.y);
+            tc_split(v[q].z, h.z, lo4.z); tc_split(v[q].w, h.w, lo4.w);
+            const size_t o = ((size_t)kc * NP + n) * 4;
+            *reinterpret_cast<float4*>(W_hi + o) = h;
+            *reinterpret_cast<float4*>(W_lo + o) = lo4;
+          }
+        }
       }
       // generic-proxy shared writes (A from the previous epilogue, W) -> visible to the tensor core
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -188,34 +238,40 @@ __global__ void __launch_bounds__(kTcThreads) mlp_tc_forward_kernel(MlpDev m, lo
       phase ^= 1u;
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     }
-    // epilogue: thread t <- accumulator row t (TMEM lane 32*warp + lane)
+    // epilogue: thread t <- accumulator row t (TMEM lane 32*warp + lane).  Padded columns need no
+    // guard: their weights and bias are zero, so they come out as act(0) = 0.
     const bool last = l == m.levels;
-    const float* Bg = m.B[l];
+    const int leaky = m.leaky;
     const int cols = tc_round16(Dout);
-    float* hs = (!last && hsave) ? hsave + (size_t)l * N * m.hidden : nullptr;
+    const float* bl = bias_s + l * kTcMaxDim;
+    float* hs = (!last && hsave && row < N) ? hsave + ((size_t)l * N + row) * Dout : nullptr;
+    float* yr = (last && row < N) ? y + row * Dout : nullptr;
     for (int c0 = 0; c0 < cols; c0 += 16) {
       uint32_t r[16];
       tc_ld16(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, r);
       float v[16];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) {
-        const int c = c0 + j;
-        float t = __uint_as_float(r[j]);
-        if (c < Dout) {
-          if (Bg) t += __ldg(Bg + c);
-          if (!last) t = mlp_act(t, m.leaky);
-        } else {
-          t = 0.f;
-        }
-        v[j] = t;
+      for (int q = 0; q < 4; ++q) {
+        const float4 b4 = *reinterpret_cast<const float4*>(bl + c0 + 4 * q);
+        v[4 * q + 0] = __uint_as_float(r[4 * q + 0]) + b4.x;
+        v[4 * q + 1] = __uint_as_float(r[4 * q + 1]) + b4.y;
+        v[4 * q + 2] = __uint_as_float(r[4 * q + 2]) + b4.z;
+        v[4 * q + 3] = __uint_as_float(r[4 * q + 3]) + b4.w;
       }
       if (last) {
-        if (row < N) {
+        if (yr) {
+          if (c0 + 16 <= Dout) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (c0 + j < Dout) y[row * m.out_dim + c0 + j] = v[j];
+            for (int j = 0; j < 16; ++j) yr[c0 + j] = v[j];
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (c0 + j < Dout) yr[c0 + j] = v[j];
+          }
         }
       } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = mlp_act(v[j], leaky);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           float4 h, lo4;
@@ -225,10 +281,15 @@ __global__ void __launch_bounds__(kTcThreads) mlp_tc_forward_kernel(MlpDev m, lo
           *reinterpret_cast<float4*>(A_hi + o) = h;
           *reinterpret_cast<float4*>(A_lo + o) = lo4;
         }
-        if (hs && row < N) {
+        if (hs) {
+          if (c0 + 16 <= Dout) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (c0 + j < Dout) hs[row * Dout + c0 + j] = v[j];
+            for (int j = 0; j < 16; ++j) hs[c0 + j] = v[j];
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (c0 + j < Dout) hs[c0 + j] = v[j];
+          }
         }
       }
     }
