@@ -48,7 +48,8 @@ def peaks() -> dict:
     if os.path.exists(p):
         with open(p) as f:
             d = json.load(f)
-        return dict(hbm_gbs=float(d["hbm_gbs"]), source="measured (MEASURED_PEAKS.json)")
+        return dict(hbm_gbs=float(d["hbm_gbs"]), bf16_tflops=float(d.get("bf16_tflops", 2250.0)),
+                    source="measured (MEASURED_PEAKS.json)")
     return dict(hbm_gbs=6650.0, source="fallback (B200_PROFILING.md)")
 
 
@@ -665,6 +666,51 @@ def sdf_cpu_leg(budget_s: float = 15.0) -> dict:
             "sample": f"full C1 scan ({q.shape[0]} queries, infer_bs 80000, no_grad), median of {len(times)} runs"}
 
 
+# ---- decoder MLP leg (extra.mlp_batch): the one dense contraction of the path ----------------------
+def mlp_leg(args, local) -> dict:
+    """Decoder.mlp_batch on a spawn_gaussians-sized batch (GR:609-714): 2^20 rows through a 35 -> 64 -> 64 -> 5
+    head, tcgen05/TMEM kernel (3xTF32) with the fp32 SIMT kernel beside it."""
+    import types
+    from pings_b200 import decoder as D
+    dev = torch.device("cuda", local)
+    cfg = types.SimpleNamespace(mlp_leaky_relu=False, infer_bs=4096, mlp_bias_on=True, main_loss_type="bce",
+                                logistic_gaussian_ratio=0.55, sigma_sigmoid_m=0.1, device=dev)
+    torch.manual_seed(0)
+    dec = D.Decoder(cfg, 32, 64, 2, 5)
+    N = 1 << 20
+    x = torch.randn(N, 35, device=dev)
+    flop = 2.0 * N * (35 * 64 + 64 * 64 + 64 * 5)
+    byts = N * (35 + 5) * 4
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def timed(impl):
+        for _ in range(max(3, args.warmup)):
+            D.mlp_forward_impl(dec, x, impl)
+        ms = 0.0
+        for _ in range(args.steps):
+            flush.fill_(1)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            D.mlp_forward_impl(dec, x, impl)
+            b.record()
+            b.synchronize()
+            ms += a.elapsed_time(b)
+        return ms / args.steps
+
+    ms_tc, ms_simt = timed(D.MLP_TCGEN05), timed(D.MLP_SIMT)
+    pk = peaks()
+    tf32_peak = pk.get("bf16_tflops", 2250.0) / 2.0
+    return {"mlp_batch": {
+        "metric": "decoder MLP rows/s (mlp_batch, 35-64-64-5, fp32-accurate)", "value": round(N / (ms_tc * 1e-3), 1),
+        "unit": "rows/s", "ms_per_step": round(ms_tc, 4), "rows": N, "simt_fp32_ms": round(ms_simt, 4),
+        "roofline": {"bound": "tensor", "kernel": "mlp_tc_forward_kernel", "achieved": round(flop / ms_tc / 1e9, 2),
+                     "peak": round(tf32_peak, 1), "unit": "TFLOP/s", "frac": round(flop / ms_tc / 1e9 / tf32_peak, 4),
+                     "note": "algorithmic fp32 FLOPs; the kernel issues 3 TF32 MMAs per algorithmic product (3xTF32 "
+                             "split) and is bound by its register epilogue (bias, activation, hi/lo split, restage), "
+                             "peak = measured bf16 dense / 2",
+                     "hbm_gbs": round(byts / ms_tc / 1e6, 1)}}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -698,6 +744,10 @@ def main():
                 line["extra"].update(surfel_leg(args, local))
             except Exception as ex:
                 line["extra"]["surfel_ssim"] = f"failed: {ex!r}"
+            try:
+                line["extra"].update(mlp_leg(args, local))
+            except Exception as ex:
+                line["extra"]["mlp_batch"] = f"failed: {ex!r}"
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_baseline_line(args)
             if cb is not None:
