@@ -16,6 +16,11 @@ bool map_ok(const PgNeuralMap* m, bool tf) {
 NpMapDev to_dev(const PgNeuralMap* m, int time_filtering) {
   NpMapDev d;
   d.buffer_size = m->buffer_size;
+  {
+    const unsigned long long bs = (unsigned long long)m->buffer_size;
+    // floor(2^64 / bs); for a power of two (2^64 - 1) / bs is one short, which the correction step absorbs
+    d.bs_magic = bs ? ~0ull / bs : 0ull;
+  }
   d.table = reinterpret_cast<const long long*>(m->buffer_pt_index);
   d.pts = m->neural_points;
   d.n_points = m->n_points;

@@ -23,6 +23,7 @@ namespace pg {
 
 struct NpMapDev {
   long long buffer_size;
+  unsigned long long bs_magic;   // floor(2^64 / buffer_size): exact remainder without the 64-bit division routine
   const long long* table;
   const float* pts;
   long long n_points;
@@ -44,8 +45,15 @@ __device__ __forceinline__ void np_probe(const NpMapDev& m, long long gx, long l
                                          float qx, float qy, float qz, long long& idx, float& dist2) {
   const long long cx = gx + m.dx[3 * k + 0], cy = gy + m.dx[3 * k + 1], cz = gz + m.dx[3 * k + 2];
   const long long h = cx * m.p0 + cy * m.p1 + cz * m.p2;
-  long long hv = h % m.buffer_size;  // torch.fmod: sign of the dividend
-  if (hv < 0) hv += m.buffer_size;   // negative index wraps (NP:1084)
+  // h % buffer_size with the sign of the dividend (torch.remainder on int64 as used at NP:1078-1084 is
+  // the C remainder), then the negative-index wrap (NP:1084).  Barrett: q = hi64(|h| * floor(2^64/d))
+  // is at most 1 below the true quotient, so r = |h| - q*d < 2d.
+  const unsigned long long d = (unsigned long long)m.buffer_size;
+  const unsigned long long ah = h < 0 ? 0ull - (unsigned long long)h : (unsigned long long)h;
+  unsigned long long r = ah - __umul64hi(ah, m.bs_magic) * d;
+  if (r >= d) r -= d;
+  if (r >= d) r -= d;
+  const long long hv = (h < 0 && r != 0) ? (long long)(d - r) : (long long)r;
   idx = m.table[hv];
   if (m.time_filtering) {
     const int ts = m.ts_create[np_wrap(idx, m.n_points)];
@@ -141,15 +149,11 @@ __device__ __forceinline__ int np_warp_knn(const NpMapDev& m, const NpQueryDev& 
         bk = c * 32 + lane;
       }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float od = __shfl_xor_sync(0xffffffffu, bd, o);
-      const int ok = __shfl_xor_sync(0xffffffffu, bk, o);
-      if (od < bd || (od == bd && ok < bk)) {
-        bd = od;
-        bk = ok;
-      }
-    }
+    // warp arg-min with two REDUX: distances are >= +0, so their bit patterns order like the values;
+    // among the lanes holding the minimum the lowest probe position wins
+    const uint32_t mn = __reduce_min_sync(0xffffffffu, __float_as_uint(bd));
+    bk = (int)__reduce_min_sync(0xffffffffu, __float_as_uint(bd) == mn ? (uint32_t)bk : 0xffffffffu);
+    bd = __uint_as_float(mn);
     const int owner = bk & 31, slot = bk >> 5;
     int oi = -1;
 #pragma unroll
