@@ -41,10 +41,21 @@ struct NpMapDev {
 __device__ __forceinline__ long long np_wrap(long long i, long long n) { return i < 0 ? i + n : i; }
 
 // One probe of the neighbourhood: returns the global index (or -1) and the squared distance.
-__device__ __forceinline__ void np_probe(const NpMapDev& m, long long gx, long long gy, long long gz, int k,
-                                         float qx, float qy, float qz, long long& idx, float& dist2) {
-  const long long cx = gx + m.dx[3 * k + 0], cy = gy + m.dx[3 * k + 1], cz = gz + m.dx[3 * k + 2];
-  const long long h = cx * m.p0 + cy * m.p1 + cz * m.p2;
+// Hash contribution of neighbourhood offset k.  int64 arithmetic wraps, so
+// (g + dx) . p == g . p + dx . p exactly and the per-offset part can be hoisted out of the query loop.
+__device__ __forceinline__ long long np_hash_delta(const NpMapDev& m, int k) {
+  return (long long)((unsigned long long)m.dx[3 * k + 0] * (unsigned long long)m.p0 +
+                     (unsigned long long)m.dx[3 * k + 1] * (unsigned long long)m.p1 +
+                     (unsigned long long)m.dx[3 * k + 2] * (unsigned long long)m.p2);
+}
+__device__ __forceinline__ long long np_hash_base(const NpMapDev& m, long long gx, long long gy, long long gz) {
+  return (long long)((unsigned long long)gx * (unsigned long long)m.p0 + (unsigned long long)gy * (unsigned long long)m.p1 +
+                     (unsigned long long)gz * (unsigned long long)m.p2);
+}
+
+// `h` = un-reduced hash of the probed cell.
+__device__ __forceinline__ void np_probe_h(const NpMapDev& m, long long h, float qx, float qy, float qz,
+                                           long long& idx, float& dist2) {
   // h % buffer_size with the sign of the dividend (torch.remainder on int64 as used at NP:1078-1084 is
   // the C remainder), then the negative-index wrap (NP:1084).  Barrett: q = hi64(|h| * floor(2^64/d))
   // is at most 1 below the true quotient, so r = |h| - q*d < 2d.
@@ -70,6 +81,12 @@ __device__ __forceinline__ void np_probe(const NpMapDev& m, long long gx, long l
 }
 
 __device__ __forceinline__ long long np_cell(float q, float res) { return (long long)floorf(__fdiv_rn(q, res)); }
+
+__device__ __forceinline__ void np_probe(const NpMapDev& m, long long gx, long long gy, long long gz, int k,
+                                         float qx, float qy, float qz, long long& idx, float& dist2) {
+  const long long h = (long long)((unsigned long long)np_hash_base(m, gx, gy, gz) + (unsigned long long)np_hash_delta(m, k));
+  np_probe_h(m, h, qx, qy, qz, idx, dist2);
+}
 
 // ---- radius_neighborhood_search: one thread per (query, probe) --------------------------------
 __global__ void __launch_bounds__(256) np_radius_search_kernel(NpMapDev m, long long N, const float* __restrict__ q,
@@ -106,10 +123,17 @@ constexpr int kNpMaxK = 32;             // nn_k <= 32 (one kept neighbour per la
 
 // Runs the probes of one query on the calling warp and leaves the nn_k nearest valid neighbours in
 // lanes [0, nn_k): (sel_d, sel_i) with sel_i the FINAL (local) index or -1. Returns nn_count.
+// Per-lane hash deltas of the probes c*32 + lane (query independent: hoist out of persistent loops).
 template <int CPL>
-__device__ __forceinline__ int np_warp_knn(const NpMapDev& m, const NpQueryDev& a, float qx, float qy, float qz,
-                                           int lane, float& sel_d, int& sel_i) {
-  const long long gx = np_cell(qx, m.res), gy = np_cell(qy, m.res), gz = np_cell(qz, m.res);
+__device__ __forceinline__ void np_lane_deltas(const NpMapDev& m, int lane, long long (&dh)[CPL]) {
+#pragma unroll
+  for (int c = 0; c < CPL; ++c) dh[c] = (c * 32 + lane < m.K) ? np_hash_delta(m, c * 32 + lane) : 0;
+}
+
+template <int CPL>
+__device__ __forceinline__ int np_warp_knn(const NpMapDev& m, const NpQueryDev& a, const long long (&dh)[CPL], float qx,
+                                           float qy, float qz, int lane, float& sel_d, int& sel_i) {
+  const long long h0 = np_hash_base(m, np_cell(qx, m.res), np_cell(qy, m.res), np_cell(qz, m.res));
   float cd[CPL];
   int ci[CPL];
   int cnt = 0;
@@ -121,7 +145,7 @@ __device__ __forceinline__ int np_warp_knn(const NpMapDev& m, const NpQueryDev& 
     if (k < m.K) {
       long long idx;
       float d;
-      np_probe(m, gx, gy, gz, k, qx, qy, qz, idx, d);
+      np_probe_h(m, (long long)((unsigned long long)h0 + (unsigned long long)dh[c]), qx, qy, qz, idx, d);
       if (idx >= 0) {
         if (a.use_only_measured && a.free_mask[idx]) idx = -1;
         if (idx >= 0 && a.use_only_valid && !a.valid_mask[idx]) idx = -1;
@@ -267,7 +291,9 @@ __global__ void __launch_bounds__(kNpWarps * 32) np_query_kernel(NpMapDev m, NpQ
   const float qx = q[3 * n], qy = q[3 * n + 1], qz = q[3 * n + 2];
   float sel_d;
   int sel_i;
-  const int cnt = np_warp_knn<CPL>(m, a, qx, qy, qz, lane, sel_d, sel_i);
+  long long dh[CPL];
+  np_lane_deltas<CPL>(m, lane, dh);
+  const int cnt = np_warp_knn<CPL>(m, a, dh, qx, qy, qz, lane, sel_d, sel_i);
   const float w = np_idw_weight(sel_d, sel_i, a.nn_k, cnt, lane);
   if (lane < a.nn_k) {
     weight[n * a.nn_k + lane] = w;

@@ -79,11 +79,13 @@ __global__ void __launch_bounds__(kSdfWarps * 32) sdf_query_kernel(NpMapDev m, N
   float* xb = xa + Dmax;
   __syncthreads();
   const int F = a.F_geo, Fo = F + 3;
+  long long dh[CPL];
+  np_lane_deltas<CPL>(m, lane, dh);
   for (long long n = (long long)blockIdx.x * kSdfWarps + warp; n < N; n += (long long)gridDim.x * kSdfWarps) {
     const float qx = q[3 * n], qy = q[3 * n + 1], qz = q[3 * n + 2];
     float sel_d;
     int sel_i;
-    const int cnt = np_warp_knn<CPL>(m, a, qx, qy, qz, lane, sel_d, sel_i);
+    const int cnt = np_warp_knn<CPL>(m, a, dh, qx, qy, qz, lane, sel_d, sel_i);
     const float w = np_idw_weight(sel_d, sel_i, a.nn_k, cnt, lane);
     if (lane == 0 && nn_counts) nn_counts[n] = cnt;
     if (a.weighted_first) {
