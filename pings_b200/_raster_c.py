@@ -125,25 +125,41 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, projmatrix_raw, tan_fovx, tan_fovy,
                                  dL_dout_color, dL_dout_depths, sh, degree, campos, geomBuffer, R, binningBuffer,
-                                 imageBuffer, debug, full_tau=False):
+                                 imageBuffer, debug, full_tau=False, param_grads_out=None):
     """R3/rasterize_points.cu:124-211.  Returns the same 9-tuple; the last element is the pose
     gradient already reduced over Gaussians as a [1,6] tensor (the reference returns [P,6] and
     sums it in Python, R3 diff_gaussian_rasterization/__init__.py:152); pass full_tau=True for
-    the per-Gaussian [P,6] layout."""
+    the per-Gaussian [P,6] layout.
+
+    param_grads_out (optional): a flat fp32 tensor of 14*P elements; the Gaussian-parameter
+    gradients are then written straight into it as [means3D 3P | colors 3P | opacity P | scales 3P |
+    rotations 4P] and returned as views, so a data-parallel caller can all-reduce one buffer without
+    a gather copy (pings_b200.parallel.FlatGradAllReduce layout)."""
     lib = L.lib()
     dev = means3D.device
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     M = sh.size(1) if sh.numel() != 0 else 0
     fopt = dict(dtype=torch.float32, device=dev)
-    dL_dmeans3D = torch.empty(P, 3, **fopt)
+    if param_grads_out is not None:
+        flat = param_grads_out
+        if flat.dtype != torch.float32 or flat.device != dev or flat.numel() != 14 * P or not flat.is_contiguous():
+            raise RuntimeError("param_grads_out must be a contiguous fp32 tensor of 14*P elements on the input device")
+        flat = flat.view(-1)
+        dL_dmeans3D = flat[0:3 * P].view(P, 3)
+        dL_dcolors = flat[3 * P:6 * P].view(P, 3)
+        dL_dopacity = flat[6 * P:7 * P].view(P, 1)
+        dL_dscales = flat[7 * P:10 * P].view(P, 3)
+        dL_drotations = flat[10 * P:14 * P].view(P, 4)
+    else:
+        dL_dmeans3D = torch.empty(P, 3, **fopt)
+        dL_dcolors = torch.empty(P, 3, **fopt)
+        dL_dopacity = torch.empty(P, 1, **fopt)
+        dL_dscales = torch.empty(P, 3, **fopt)
+        dL_drotations = torch.empty(P, 4, **fopt)
     dL_dmeans2D = torch.empty(P, 3, **fopt)
-    dL_dcolors = torch.empty(P, 3, **fopt)
-    dL_dopacity = torch.empty(P, 1, **fopt)
     dL_dcov3D = torch.empty(P, 6, **fopt)
     dL_dsh = torch.empty(P, M, 3, **fopt)
-    dL_dscales = torch.empty(P, 3, **fopt)
-    dL_drotations = torch.empty(P, 4, **fopt)
     dL_dtau = torch.zeros(1, 6, **fopt)
     tau_full = torch.empty(P, 6, **fopt) if full_tau else None
     if P != 0:
@@ -235,14 +251,25 @@ def rasterize_gaussians_surfel_backward(background, means3D, radii, colors, scal
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     M = sh.size(1) if sh.numel() != 0 else 0
     fopt = dict(dtype=torch.float32, device=dev)
-    dL_dmeans3D = torch.empty(P, 3, **fopt)
+    if param_grads_out is not None:
+        flat = param_grads_out
+        if flat.dtype != torch.float32 or flat.device != dev or flat.numel() != 14 * P or not flat.is_contiguous():
+            raise RuntimeError("param_grads_out must be a contiguous fp32 tensor of 14*P elements on the input device")
+        flat = flat.view(-1)
+        dL_dmeans3D = flat[0:3 * P].view(P, 3)
+        dL_dcolors = flat[3 * P:6 * P].view(P, 3)
+        dL_dopacity = flat[6 * P:7 * P].view(P, 1)
+        dL_dscales = flat[7 * P:10 * P].view(P, 3)
+        dL_drotations = flat[10 * P:14 * P].view(P, 4)
+    else:
+        dL_dmeans3D = torch.empty(P, 3, **fopt)
+        dL_dcolors = torch.empty(P, 3, **fopt)
+        dL_dopacity = torch.empty(P, 1, **fopt)
+        dL_dscales = torch.empty(P, 3, **fopt)
+        dL_drotations = torch.empty(P, 4, **fopt)
     dL_dmeans2D = torch.empty(P, 3, **fopt)
-    dL_dcolors = torch.empty(P, 3, **fopt)
-    dL_dopacity = torch.empty(P, 1, **fopt)
     dL_dcov3D = torch.empty(P, 6, **fopt)
     dL_dsh = torch.empty(P, M, 3, **fopt)
-    dL_dscales = torch.empty(P, 3, **fopt)
-    dL_drotations = torch.empty(P, 4, **fopt)
     dL_dtau = torch.zeros(1, 6, **fopt)
     tau_full = torch.empty(P, 6, **fopt) if full_tau else None
     if P != 0:

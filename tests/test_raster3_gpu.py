@@ -85,6 +85,16 @@ def test_forward_bitexact_and_backward(P, W, H, seed):
                                            ct["color"], ct["depth"], e, 0, center, geom, R, binning, img, False)
     tau_ref = g["tau"].double().sum(0)
     assert _relmax(out2[-1].flatten(), tau_ref) < 1e-4
+    # flat output buffer for the data-parallel exchange: same values, laid out [means3D|colors|opacity|scales|rotations]
+    flat = torch.full((14 * P,), float("nan"), device=sc["means3D"].device)
+    out3 = RC.rasterize_gaussians_backward(bg, sc["means3D"], radii, sc["colors_precomp"], sc["scales"],
+                                           sc["rotations"], 1.0, e, view, full, proj, cam.tanfovx, cam.tanfovy,
+                                           ct["color"], ct["depth"], e, 0, center, geom, R, binning, img, False,
+                                           param_grads_out=flat)
+    expect = torch.cat([out3[3].flatten(), out3[1].flatten(), out3[2].flatten(), out3[6].flatten(), out3[7].flatten()])
+    assert torch.equal(flat, expect) and out3[3].data_ptr() == flat.data_ptr()
+    for a, b in zip((out3[3], out3[1], out3[2], out3[6], out3[7]), (out2[3], out2[1], out2[2], out2[6], out2[7])):
+        assert _relmax(a, b) < 1e-5   # float atomics: run-to-run noise only
 
 
 def test_sh_and_cov3d_precomp_paths():
