@@ -250,6 +250,8 @@ def run_ours(args, rank, world, local):
     # ---- e2e through the public API with host buffers ----
     pinned = {k: v.contiguous().pin_memory() for k, v in sc_cpu.items()}
     target = target_cpu.to(dev)
+    target_depth = torch.rand(1, H, W, generator=torch.Generator().manual_seed(78)).mul_(60.0).add_(1.0).to(dev)
+    from pings_b200.losses import photo_depth_loss
     h2d_bytes = sum(v.numel() * v.element_size() for v in pinned.values())
     host_out = [torch.empty(7, dtype=torch.float32).pin_memory() for _ in range(2)]
     out_done = [torch.cuda.Event() for _ in range(2)]
@@ -288,7 +290,8 @@ def run_ours(args, rank, world, local):
         color, radii, depth, opacity, n_touched = rast(leaves["means3D"], m2d, leaves["opacities"],
                                                        colors_precomp=leaves["colors_precomp"], scales=leaves["scales"],
                                                        rotations=leaves["rotations"], theta=theta, rho=rho)
-        loss = (color - target).abs().mean() + 0.01 * depth.mean()
+        # the mapping loss of utils/mapper.py:1239,1252-1267 (photometric L1 + masked depth L1), fused op
+        loss, _, _ = photo_depth_loss(color, target, depth, target_depth, opacity, 0.01, 0.5, 80.0, 0.5)
         loss.backward()
         consumed[slot].record(cur)
         if world > 1:

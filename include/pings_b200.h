@@ -265,6 +265,22 @@ int pg_sdf_query(const PgNeuralMap* map, const PgQueryArgs* args, const PgMlp* m
                  const float* query_xyz, float* sdf, float* sdf_std, int64_t* nn_counts, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Post-raster loss assembly (utils/mapper.py:1239,1252-1267): loss = mean|rgb - gt_rgb| +
+ * lambda_depth * mean over valid pixels of |gt_depth - depth| (or |1/gt_depth - 1/depth| when
+ * inverse_depth), valid = depth_min < gt_depth < depth_max [and alpha > min_alpha].  depth/gt_depth
+ * /alpha may be NULL (no depth term / no alpha mask).  The forward also writes the backward seeds
+ * (seed_rgb [3,H,W], seed_depth [H,W]) and the reduction scalars sums[3] (double); loss[3] =
+ * {total, rgb l1, depth l1}.  The backward scales the seeds by *upstream (device scalar).
+ * ---------------------------------------------------------------------------------------- */
+int pg_photo_depth_loss_forward(int H, int W, const float* rgb, const float* gt_rgb, const float* depth,
+                                const float* gt_depth, const float* alpha, float lambda_depth, float depth_min,
+                                float depth_max, float min_alpha, int inverse_depth, float* seed_rgb, float* seed_depth,
+                                double* sums, float* loss, void* stream);
+int pg_photo_depth_loss_backward(int H, int W, float lambda_depth, const float* upstream, const double* sums,
+                                 const float* seed_rgb, const float* seed_depth, float* d_rgb, float* d_depth,
+                                 void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Fused SSIM (FS/ssim.h:7-26: fusedssim, fusedssim_backward).  img*: [B,C,H,W] contiguous fp32.
  * dm_* may be NULL in the forward (train == false, FS/ssim.cu:458-460).  In the backward dL_dmap
  * may be NULL, in which case the map gradient is the constant dL_dmap_scalar (the backward of the

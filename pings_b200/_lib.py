@@ -122,6 +122,11 @@ def lib() -> C.CDLL:
     L.pg_raster_debug_views.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, fp, fp, fp] + [C.POINTER(fp)] * 6
     L.pg_raster_band_records.restype = C.c_int64
     L.pg_raster_band_records.argtypes = [C.c_int, C.c_int, C.c_int64, fp, fp]
+    L.pg_photo_depth_loss_forward.restype = C.c_int
+    L.pg_photo_depth_loss_forward.argtypes = [C.c_int, C.c_int, fp, fp, fp, fp, fp, C.c_float, C.c_float, C.c_float,
+                                              C.c_float, C.c_int, fp, fp, fp, fp, fp]
+    L.pg_photo_depth_loss_backward.restype = C.c_int
+    L.pg_photo_depth_loss_backward.argtypes = [C.c_int, C.c_int, C.c_float, fp, fp, fp, fp, fp, fp, fp]
     L.pg_np_radius_search.restype = C.c_int
     L.pg_np_radius_search.argtypes = [C.POINTER(PgNeuralMap), C.c_int64, fp, C.c_int, fp, fp, fp]
     L.pg_np_query_feature.restype = C.c_int

@@ -1,5 +1,6 @@
 // C-ABI entry points of fused SSIM (see include/pings_b200.h).
 #include "pg_ssim.cuh"
+#include "pg_imgops.cuh"
 
 using namespace pg;
 
@@ -34,6 +35,39 @@ int pg_ssim_backward(int B, int C, int H, int W, float C1, float C2, const float
   Phase ph("ssim_bwd", st);
   ssim_bwd_kernel<<<grid, kSsThreads, 0, st>>>(H, W, img1, img2, dL_dmap, dL_dmap_scalar, dm_dmu1, dm_dsigma1_sq,
                                               dm_dsigma12, dL_dimg1);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_photo_depth_loss_forward(int H, int W, const float* rgb, const float* gt_rgb, const float* depth,
+                                const float* gt_depth, const float* alpha, float lambda_depth, float depth_min,
+                                float depth_max, float min_alpha, int inverse_depth, float* seed_rgb, float* seed_depth,
+                                double* sums, float* loss, void* stream) {
+  if (H <= 0 || W <= 0 || !rgb || !gt_rgb || !seed_rgb || !sums || !loss) return PG_ERR_ARG;
+  if (depth && (!gt_depth || !seed_depth)) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  PhotoDepthArgs a;
+  a.HW = H * W; a.rgb = rgb; a.gt_rgb = gt_rgb; a.depth = depth; a.gt_depth = gt_depth; a.alpha = alpha;
+  a.depth_min = depth_min; a.depth_max = depth_max; a.min_alpha = min_alpha; a.inverse_depth = inverse_depth;
+  PG_CUDA(cudaMemsetAsync(sums, 0, 3 * sizeof(double), st));
+  Phase ph("photo_depth_loss_fwd", st);
+  const int blocks = min(div_up(a.HW, 256), 148 * 8);
+  photo_depth_fwd_kernel<<<blocks, 256, 0, st>>>(a, seed_rgb, seed_depth, sums);
+  photo_depth_finish_kernel<<<1, 1, 0, st>>>(a.HW, depth ? lambda_depth : 0.f, sums, loss);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_photo_depth_loss_backward(int H, int W, float lambda_depth, const float* upstream, const double* sums,
+                                 const float* seed_rgb, const float* seed_depth, float* d_rgb, float* d_depth,
+                                 void* stream) {
+  if (H <= 0 || W <= 0 || !upstream || !sums || !seed_rgb || !d_rgb) return PG_ERR_ARG;
+  if (d_depth && !seed_depth) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  Phase ph("photo_depth_loss_bwd", st);
+  const int HW = H * W;
+  photo_depth_bwd_kernel<<<min(div_up(HW, 256), 148 * 8), 256, 0, st>>>(HW, lambda_depth, upstream, sums, seed_rgb,
+                                                                          seed_depth, d_rgb, d_depth);
   PG_LAUNCH_CHECK(0, st);
   return PG_OK;
 }
