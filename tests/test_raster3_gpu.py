@@ -229,3 +229,35 @@ def test_cpu_oracle_vs_reference_and_ours():
     for n in ("means2D", "colors", "opacity", "means3D", "cov3D", "scales", "rotations", "tau"):
         assert _relmax(cg[n], g[n].cpu()) < 1e-2, ("cpu-vs-ref", n)
         assert _relmax(cg[n], mine[n].cpu()) < 1e-2, ("cpu-vs-ours", n)
+
+
+# Binning edge cases: tall / wide tile grids (one band vs several), Gaussians that cover whole bands (segments
+# denser than the shared-memory stage -> per-group staging), a cloud of sub-tile Gaussians (1 record = 1 tile),
+# and P above one cooperative-sort CTA wave boundary (4096-key chunks, ragged last chunk).
+@pytest.mark.parametrize("P,W,H,seed,scale_mul", [
+    (3000, 640, 360, 11, 40.0),     # every Gaussian covers most of the image: dense segments
+    (120000, 640, 360, 12, 0.05),   # tiny Gaussians
+    (20000, 48, 2000, 13, 1.0),     # tall: 3 x 125 tiles, one band per row
+    (20000, 3000, 100, 14, 3.0),    # wide: 188 x 7 tiles, six bands per row
+    (4097, 33, 17, 15, 1.0),        # 3 x 2 tiles, ragged everything
+    (1300000, 320, 200, 16, 0.3),   # more Gaussians than the cooperative depth sort holds: multi-kernel sort path
+])
+def test_binning_lists_bitexact_edge_cases(P, W, H, seed, scale_mul):
+    from oracle.ref_api import RefRaster3, available
+    from pings_b200 import _raster_c as RC
+    if not available("ref_r3"):
+        pytest.fail("oracle/_ref/libref_r3.so missing: run __graft_entry__.build() where /root/reference exists")
+    cam, sc, mats, ct = _scene(P, W, H, seed)
+    sc["scales"] = (sc["scales"] * scale_mul).contiguous()
+    view, full, proj, center = mats
+    bg = torch.zeros(3, device="cuda")
+    R, color, radii, geom, binning, img, depth, opac, n_touched = _mine_forward(cam, sc, mats, W, H, bg, debug=True)
+    ref = RefRaster3()
+    r = ref.forward(sc, (view, full, proj), W, H, cam.tanfovx, cam.tanfovy, bg, campos=center)
+    assert R == r["num_rendered"] and R > 0
+    dv = RC.debug_views(0, P, W, H, R, geom, binning, img)
+    assert torch.equal(radii, r["radii"])
+    assert torch.equal(dv["point_list"], r["point_list"])
+    assert torch.equal(dv["ranges"], r["ranges"])
+    assert torch.equal(dv["n_contrib"], r["n_contrib"])
+    torch.testing.assert_close(color, r["color"], rtol=IMG_RTOL, atol=IMG_ATOL)
