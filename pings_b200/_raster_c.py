@@ -242,9 +242,9 @@ def rasterize_gaussians_surfel_backward(background, means3D, radii, colors, scal
                                         cov3D_precomp, viewmatrix, projmatrix, projmatrix_raw, prcppoint, patchbbox,
                                         tan_fovx, tan_fovy, dL_dout_color, dL_dout_normal, dL_dout_depth, dL_dout_opac,
                                         sh, degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, config,
-                                        full_tau=False):
+                                        full_tau=False, param_grads_out=None):
     """RS/rasterize_points.cu:133-233.  Same 9-tuple; the pose gradient is already reduced to [1,6]
-    unless full_tau=True (see rasterize_gaussians_backward)."""
+    unless full_tau=True; param_grads_out as in rasterize_gaussians_backward."""
     lib = L.lib()
     dev = means3D.device
     P = means3D.size(0)
