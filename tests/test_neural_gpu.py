@@ -124,3 +124,30 @@ def test_large_scan_vs_oracle_and_properties():
     perm = torch.randperm(q.shape[0], device="cuda")
     sdf_p, _, _ = npm.sdf_fused(q[perm], dec)
     assert torch.equal(sdf_p, sdf[perm])
+
+
+def test_sdf_query_mirror_paths_agree():
+    """pings_b200.sdf_ops.SdfQuery (Mapper.sdf / sdf_batch / get_numerical_gradient, utils/mapper.py:2273-2369):
+    the fused no_grad kernel, the autograd composition and the chunked batch variant give the same SDF; the
+    numerical gradient equals central differences of sdf() evaluated point by point."""
+    from pings_b200 import synth_neural as SN
+    from pings_b200.sdf_ops import SdfQuery
+    npm, dec, q = SN.c1_map_and_queries(device="cuda", n_az=200)
+    sq = SdfQuery(npm, dec)
+    q = q[:20000]
+    with torch.no_grad():
+        s_fused, _, valid_fused = sq.sdf(q)
+    s_grad, _, valid_grad = sq.sdf(q.clone())                     # grad mode: query_feature + decoder
+    s_batch, _, valid_batch = sq.sdf_batch(q, 4096)
+    assert torch.equal(valid_fused, valid_grad) and torch.equal(valid_fused, valid_batch)
+    np.testing.assert_allclose(s_fused.cpu().numpy(), s_grad.detach().cpu().numpy(), rtol=RTOL, atol=ATOL)
+    # chunks below 4096 rows take the SIMT decoder, larger ones the tcgen05 one: fp32-level differences only
+    np.testing.assert_allclose(s_batch.detach().cpu().numpy(), s_grad.detach().cpu().numpy(), rtol=RTOL, atol=ATOL)
+    with torch.no_grad():
+        g2 = sq.get_numerical_gradient(q[:512], eps=0.02, two_side=True)
+        e = torch.tensor([0.02, 0.0, 0.0], device="cuda")
+        gx = (sq.sdf(q[:512] + e)[0] - sq.sdf(q[:512] - e)[0]) / 0.04
+        assert torch.equal(g2[:, 0], gx)
+        g1 = sq.get_numerical_gradient(q[:512], sdf_x=s_fused[:512], eps=0.02, two_side=False)
+        assert torch.equal(g1[:, 0], (sq.sdf(q[:512] + e)[0] - s_fused[:512]) / 0.02)
+        assert g2.shape == (512, 3) and g1.shape == (512, 3)
