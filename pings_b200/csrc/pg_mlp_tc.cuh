@@ -301,7 +301,239 @@ __global__ void __launch_bounds__(kTcThreads) mlp_tc_forward_kernel(MlpDev m, lo
   }
 }
 
+// ---- v2: persistent CTAs, resident weights, two tiles in flight ------------------------------------
+// When all layers' split weights fit next to two activation tiles (hidden <= 64), a CTA of 256 threads
+// stages the weights ONCE, then its two 4-warp groups each stride over 128-row tiles on their own
+// (own activation buffers, own TMEM columns, own mbarrier, named barriers instead of __syncthreads):
+// while one group runs its register epilogue the other group's MMA or input loads are in flight.
+constexpr int kTc2Threads = 256;
+
+// float offset of layer l's resident weights (hi; lo follows at +tc2_w_floats) and total per half
+__host__ __device__ inline size_t tc2_w_offset(const MlpDev& m, int layer) {
+  size_t o = 0;
+  for (int l = 0; l < layer; ++l) o += (size_t)tc_round16(mlp_layer_out(m, l)) * tc_round8(mlp_layer_in(m, l));
+  return o;
+}
+__host__ __device__ inline size_t tc2_w_floats(const MlpDev& m) { return tc2_w_offset(m, m.levels + 1); }
+__host__ __device__ inline size_t tc2_smem_bytes(const MlpDev& m) {
+  const size_t k = (size_t)tc_kmax(m);
+  return 2 * tc2_w_floats(m) * 4 + 2 * 2 * k * kTcRows * 4 + (size_t)PG_MLP_MAX_LAYERS * kTcMaxDim * 4 + 64;
+}
+inline bool tc2_supported(const MlpDev& m) {
+  return tc_supported(m) && m.hidden <= kTcPiece && tc_tmem_cols(m) <= 64 && tc2_smem_bytes(m) <= 227 * 1024;
+}
+
+__device__ __forceinline__ void tc2_group_sync(int g) {
+  asm volatile("bar.sync %0, %1;" ::"r"(g + 1), "r"(kTcThreads) : "memory");
+}
+
+template <int COLS>
+__global__ void __launch_bounds__(kTc2Threads) mlp_tc2_forward_kernel(MlpDev m, long long N, const float* __restrict__ x,
+                                                                      float* __restrict__ y, float* __restrict__ hsave) {
+  extern __shared__ __align__(128) unsigned char tc_sm[];
+  const int tid = threadIdx.x, g = tid >> 7, t = tid & 127, wg = (tid >> 5) & 3;
+  const int kmax = tc_kmax(m);
+  const size_t wfl = tc2_w_floats(m);
+  float* Wr_hi = reinterpret_cast<float*>(tc_sm);
+  float* Wr_lo = Wr_hi + wfl;
+  float* A_hi = Wr_lo + wfl + (size_t)g * 2 * kmax * kTcRows;
+  float* A_lo = A_hi + (size_t)kmax * kTcRows;
+  float* bias_s = Wr_lo + wfl + (size_t)4 * kmax * kTcRows;
+  uint64_t* mbar = reinterpret_cast<uint64_t*>(bias_s + PG_MLP_MAX_LAYERS * kTcMaxDim);   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(mbar + 2);
+
+  if ((tid >> 5) == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc_smem_u32(tmem_slot)),
+                 "n"(2 * COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  for (int i = tid; i < (m.levels + 1) * kTcMaxDim; i += kTc2Threads) {
+    const int l = i / kTcMaxDim, c = i % kTcMaxDim;
+    bias_s[i] = (m.B[l] && c < mlp_layer_out(m, l)) ? __ldg(m.B[l] + c) : 0.f;
+  }
+  if (tid < 2) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(tc_smem_u32(mbar + tid)) : "memory");
+  if (tid == 0) asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  // resident weights: every layer as [kp/4][NP][4] hi / lo (one piece per layer: Dout <= 64)
+  for (int l = 0; l <= m.levels; ++l) {
+    const int Din = mlp_layer_in(m, l), Dout = mlp_layer_out(m, l);
+    const int kp = tc_round8(Din), NP = tc_round16(Dout);
+    const float* Wg = m.W[l];
+    float* wh = Wr_hi + tc2_w_offset(m, l);
+    float* wl = Wr_lo + tc2_w_offset(m, l);
+    const int chunks = NP * (kp >> 2);
+    const float inv_np = 1.0f / (float)NP;
+    for (int i = tid; i < chunks; i += kTc2Threads) {
+      const int kc = (int)(((float)i + 0.5f) * inv_np), n = i - kc * NP;
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k = kc * 4 + j;
+        v[j] = (n < Dout && k < Din) ? __ldg(Wg + (size_t)n * Din + k) : 0.f;
+      }
+      float4 h, lo4;
+      tc_split(v[0], h.x, lo4.x); tc_split(v[1], h.y, lo4.y); tc_split(v[2], h.z, lo4.z); tc_split(v[3], h.w, lo4.w);
+      *reinterpret_cast<float4*>(wh + (size_t)i * 4) = h;    // i == kc * NP + n
+      *reinterpret_cast<float4*>(wl + (size_t)i * 4) = lo4;
+    }
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *tmem_slot + (uint32_t)(g * COLS);
+  const uint32_t mbar_a = tc_smem_u32(mbar + g);
+  const int leaky = m.leaky;
+  const long long tiles = (N + kTcRows - 1) / kTcRows;
+  uint32_t phase = 0;
+  for (long long tile = (long long)blockIdx.x * 2 + g; tile < tiles; tile += (long long)gridDim.x * 2) {
+    const long long row0 = tile * kTcRows, row = row0 + t;
+    {
+      const int Din = m.in_dim, kp = tc_round8(Din);
+      const int total = kTcRows * Din;
+      const long long left = (N - row0) * Din;
+      const int valid = left < total ? (int)left : total;
+      const float* xb = x + row0 * Din;
+      const float inv_din = 1.0f / (float)Din;
+      for (int i0 = 0; i0 < total; i0 += kTcThreads * 8) {
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int i = i0 + j * kTcThreads + t;
+          v[j] = i < valid ? __ldg(xb + i) : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int i = i0 + j * kTcThreads + t;
+          if (i < total) {
+            const int r = (int)(((float)i + 0.5f) * inv_din), k = i - r * Din;
+            float h, lo;
+            tc_split(v[j], h, lo);
+            const size_t o = ((size_t)(k >> 2) * kTcRows + r) * 4 + (k & 3);
+            A_hi[o] = h;
+            A_lo[o] = lo;
+          }
+        }
+      }
+      for (int k = Din; k < kp; ++k) {
+        const size_t o = ((size_t)(k >> 2) * kTcRows + t) * 4 + (k & 3);
+        A_hi[o] = 0.f;
+        A_lo[o] = 0.f;
+      }
+    }
+    for (int l = 0; l <= m.levels; ++l) {
+      const int Din = mlp_layer_in(m, l), Dout = mlp_layer_out(m, l);
+      const int kp = tc_round8(Din), NP = tc_round16(Dout);
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      tc2_group_sync(g);
+      if (t == 0) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t idesc = tc_idesc(NP);
+        const uint32_t a_hi = tc_smem_u32(A_hi), a_lo = tc_smem_u32(A_lo);
+        const uint32_t w_hi = tc_smem_u32(Wr_hi + tc2_w_offset(m, l)), w_lo = tc_smem_u32(Wr_lo + tc2_w_offset(m, l));
+        const uint32_t a_lbo = kTcRows * 16, w_lbo = (uint32_t)NP * 16;
+        for (int ks = 0; ks < (kp >> 3); ++ks) {
+          const uint32_t ao = (uint32_t)ks * 2u * a_lbo, wo = (uint32_t)ks * 2u * w_lbo;
+          const uint64_t dah = tc_desc(a_hi + ao, a_lbo, 128), dal = tc_desc(a_lo + ao, a_lbo, 128);
+          const uint64_t dwh = tc_desc(w_hi + wo, w_lbo, 128), dwl = tc_desc(w_lo + wo, w_lbo, 128);
+          tc_mma(tmem, dah, dwh, idesc, ks > 0 ? 1u : 0u);
+          tc_mma(tmem, dal, dwh, idesc, 1u);
+          tc_mma(tmem, dah, dwl, idesc, 1u);
+        }
+        tc_commit(mbar_a);
+      }
+      tc_mbar_wait(mbar_a, phase);
+      phase ^= 1u;
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const bool last = l == m.levels;
+      const int cols = NP;
+      const float* bl = bias_s + l * kTcMaxDim;
+      float* hs = (!last && hsave && row < N) ? hsave + ((size_t)l * N + row) * Dout : nullptr;
+      float* yr = (last && row < N) ? y + row * Dout : nullptr;
+      for (int c0 = 0; c0 < cols; c0 += 16) {
+        uint32_t r[16];
+        tc_ld16(tmem + ((uint32_t)(wg * 32) << 16) + (uint32_t)c0, r);
+        float v[16];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const float4 b4 = *reinterpret_cast<const float4*>(bl + c0 + 4 * q);
+          v[4 * q + 0] = __uint_as_float(r[4 * q + 0]) + b4.x;
+          v[4 * q + 1] = __uint_as_float(r[4 * q + 1]) + b4.y;
+          v[4 * q + 2] = __uint_as_float(r[4 * q + 2]) + b4.z;
+          v[4 * q + 3] = __uint_as_float(r[4 * q + 3]) + b4.w;
+        }
+        if (last) {
+          if (yr) {
+            if (c0 + 16 <= Dout) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) yr[c0 + j] = v[j];
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (c0 + j < Dout) yr[c0 + j] = v[j];
+            }
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = mlp_act(v[j], leaky);
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            float4 h, lo4;
+            tc_split(v[4 * q + 0], h.x, lo4.x); tc_split(v[4 * q + 1], h.y, lo4.y);
+            tc_split(v[4 * q + 2], h.z, lo4.z); tc_split(v[4 * q + 3], h.w, lo4.w);
+            const size_t o = ((size_t)((c0 >> 2) + q) * kTcRows + t) * 4;
+            *reinterpret_cast<float4*>(A_hi + o) = h;
+            *reinterpret_cast<float4*>(A_lo + o) = lo4;
+          }
+          if (hs) {
+            if (c0 + 16 <= Dout) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) hs[c0 + j] = v[j];
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (c0 + j < Dout) hs[c0 + j] = v[j];
+            }
+          }
+        }
+      }
+    }
+    // the next tile's staging overwrites A: every thread of the group must be done reading TMEM / writing A
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    tc2_group_sync(g);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if ((tid >> 5) == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(*tmem_slot), "n"(2 * COLS) : "memory");
+  }
+}
+
 inline cudaError_t mlp_tc_forward(const MlpDev& m, long long N, const float* x, float* y, float* hsave, cudaStream_t st) {
+  if (tc2_supported(m) && N > 2 * kTcRows) {
+    static int sms = 0;
+    if (!sms) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      if (sms <= 0) sms = 148;
+    }
+    const size_t smem2 = tc2_smem_bytes(m);
+    const long long tiles = (N + kTcRows - 1) / kTcRows;
+    const unsigned grid2 = (unsigned)((tiles + 1) / 2 < sms ? (tiles + 1) / 2 : sms);
+    cudaError_t e2;
+    if (tc_tmem_cols(m) <= 32) {
+      e2 = cudaFuncSetAttribute(mlp_tc2_forward_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+      if (e2 != cudaSuccess) return e2;
+      mlp_tc2_forward_kernel<32><<<grid2, kTc2Threads, smem2, st>>>(m, N, x, y, hsave);
+    } else {
+      e2 = cudaFuncSetAttribute(mlp_tc2_forward_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+      if (e2 != cudaSuccess) return e2;
+      mlp_tc2_forward_kernel<64><<<grid2, kTc2Threads, smem2, st>>>(m, N, x, y, hsave);
+    }
+    return cudaGetLastError();
+  }
   const size_t smem = tc_smem_bytes(m);
   const unsigned grid = (unsigned)((N + kTcRows - 1) / kTcRows);
   const int cols = tc_tmem_cols(m);
