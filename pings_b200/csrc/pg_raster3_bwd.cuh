@@ -184,7 +184,10 @@ __global__ void __launch_bounds__(kRThreads) r3_render_bwd_kernel(
           for (int k = 0; k < 4; ++k) {
             if (act[k]) {
               const float alpha = al[k];
-              T[k] = T[k] / (1.f - alpha);
+              // one correctly rounded reciprocal serves both divisions by (1 - alpha) of R3 backward.cu:672,719
+              // (<= 1 ulp from the quotients; far inside the gradient tolerance)
+              const float inv1ma = __frcp_rn(1.f - alpha);
+              T[k] = T[k] * inv1ma;
               const float dchannel_dcolor = alpha * T[k];
               float dL_dalpha = 0.0f;
 #pragma unroll
@@ -200,7 +203,7 @@ __global__ void __launch_bounds__(kRThreads) r3_render_bwd_kernel(
               v[6] += dchannel_dcolor * dpd[k];
               dL_dalpha *= T[k];
               lalpha[k] = alpha;
-              dL_dalpha += (-Tfin[k] / (1.f - alpha)) * bgdot[k];
+              dL_dalpha += (-Tfin[k] * inv1ma) * bgdot[k];
               const float dL_dG = co.w * dL_dalpha;
               const float gdx = G[k] * ddx[k], gdy = G[k] * ddy[k];
               const float dG_ddelx = -gdx * co.x - gdy * co.y;

@@ -177,7 +177,8 @@ __global__ void __launch_bounds__(kRThreads) rs_render_bwd_kernel(
           for (int k = 0; k < 4; ++k) {
             if (act[k]) {
               const float alpha = al[k];
-              T[k] = T[k] / (1.f - alpha);
+              const float inv1ma = __frcp_rn(1.f - alpha);   // shared by the divisions of RS backward.cu (see R3 kernel)
+              T[k] = T[k] * inv1ma;
               const float dchannel_dcolor = alpha * T[k];
               float dL_dalpha = 0.0f;
 #pragma unroll
@@ -212,8 +213,8 @@ __global__ void __launch_bounds__(kRThreads) rs_render_bwd_kernel(
               dL_dalpha *= T[k];
               dL_dalpha += dpo[k] * Tfin[k] / (1 - alpha);
               lalpha[k] = alpha;
-              dL_dalpha += (-Tfin[k] / (1.f - alpha)) * bgdot[k];
-              if (!normalize_depth) dL_dalpha += (-Tfin[k] / (1.f - alpha)) * (10 * dpd[k]);
+              dL_dalpha += (-Tfin[k] * inv1ma) * bgdot[k];
+              if (!normalize_depth) dL_dalpha += (-Tfin[k] * inv1ma) * (10 * dpd[k]);
               const float dL_ddist = dL_dalpha * co.w * -0.5f * G[k];
               v[0] += dL_ddist * 2 * (co.x * ddx[k] + co.y * ddy[k]) * ddelx_dx;
               v[1] += dL_ddist * 2 * (co.z * ddy[k] + co.y * ddx[k]) * ddely_dy;

