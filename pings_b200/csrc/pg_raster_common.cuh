@@ -404,7 +404,7 @@ inline cudaError_t depth_order_and_offsets(const GeomWs& ws, int P, bool fast, c
   if (depth_sort_coop_fits(nblk)) {
     DepthSortArgs a;
     a.dkey = ws.dkey; a.keyA = ws.keyA; a.valA = ws.valA; a.keyB = ws.keyB; a.valB = ws.sorted_idx;
-    a.hist = ws.sort_scratch; a.bsum = ws.sort_scratch + (size_t)2 * nblk * 256;
+    a.hist = ws.sort_scratch; a.bsum = ws.sort_scratch + (size_t)2 * nblk * 256; a.dtot = a.bsum + nblk;
     a.wsrc = fast ? ws.wts : ws.tiles; a.rect = ws.rect; a.srect = ws.srect; a.offsets = ws.offsets;
     a.total_out = fast ? ws.wtotal : nullptr;
     a.n = n; a.nblk = nblk;
