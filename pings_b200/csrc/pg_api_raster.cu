@@ -116,7 +116,7 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
   // depth ordering runs while the host waits for the count
   {
     Phase ph("depth_sort", st);
-    PG_CUDA(depth_order_and_offsets(ws, P, bin_fast_path(gx * gy), st));
+    PG_CUDA(depth_order_and_offsets(ws, P, bin_fast_path(gx * gy), st, /*need_offsets=*/!band_path(gx, gy)));
   }
   PG_LAUNCH_CHECK(prm->debug, st);
   PG_CUDA(cudaEventSynchronize(g_slot.ev));

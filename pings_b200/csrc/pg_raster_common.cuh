@@ -397,7 +397,7 @@ __global__ void __launch_bounds__(256) gather_rect_kernel(int P, const uint32_t*
 // Depth argsort + offsets (stage 1 tail).  Leaves Gaussian ids in ws.sorted_idx.
 // `offsets` = exclusive scan in depth order of the binning weights (counting path; total -> ws.wtotal)
 // or of the tile counts (radix path).
-inline cudaError_t depth_order_and_offsets(const GeomWs& ws, int P, bool fast, cudaStream_t st) {
+inline cudaError_t depth_order_and_offsets(const GeomWs& ws, int P, bool fast, cudaStream_t st, bool need_offsets = true) {
   cudaError_t e;
   const uint32_t n = (uint32_t)P;
   const uint32_t nblk = sort_num_blocks(n);
@@ -405,7 +405,7 @@ inline cudaError_t depth_order_and_offsets(const GeomWs& ws, int P, bool fast, c
     DepthSortArgs a;
     a.dkey = ws.dkey; a.keyA = ws.keyA; a.valA = ws.valA; a.keyB = ws.keyB; a.valB = ws.sorted_idx;
     a.hist = ws.sort_scratch; a.bsum = ws.sort_scratch + (size_t)2 * nblk * 256; a.dtot = a.bsum + nblk;
-    a.wsrc = fast ? ws.wts : ws.tiles; a.rect = ws.rect; a.srect = ws.srect; a.offsets = ws.offsets;
+    a.wsrc = need_offsets ? (fast ? ws.wts : ws.tiles) : nullptr; a.rect = ws.rect; a.srect = ws.srect; a.offsets = ws.offsets;
     a.total_out = fast ? ws.wtotal : nullptr;
     a.n = n; a.nblk = nblk;
     return depth_sort_coop(a, st);
@@ -420,6 +420,7 @@ inline cudaError_t depth_order_and_offsets(const GeomWs& ws, int P, bool fast, c
   e = radix_pass<uint32_t, false, false>(ws.keyA, ws.valA, ws.keyB, ws.sorted_idx, n, 24, 8, ws.sort_scratch, st);
   if (e != cudaSuccess) return e;
   gather_rect_kernel<<<div_up(P, 256), 256, 0, st>>>(P, ws.sorted_idx, ws.rect, ws.srect);
+  if (!need_offsets) return cudaGetLastError();
   if (fast) return exclusive_scan_u32(ws.wts, ws.sorted_idx, n, ws.offsets, ws.sort_scratch, ws.wtotal, st);
   return exclusive_scan_u32(ws.tiles, ws.sorted_idx, n, ws.offsets, ws.sort_scratch, nullptr, st);
 }

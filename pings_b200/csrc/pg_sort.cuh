@@ -311,7 +311,7 @@ struct DepthSortArgs {
   uint32_t* hist;         // [2][nblk][256] double-buffered histogram matrix
   uint32_t* bsum;         // [nblk] tail scan block sums
   uint32_t* dtot;         // [2][256] digit totals of the current pass
-  const uint32_t* wsrc;   // [n] per-item weight, gathered through the argsort
+  const uint32_t* wsrc;   // [n] per-item weight, gathered through the argsort (NULL: skip the scan)
   const uint2* rect;      // [n] per-item rect, gathered through the argsort
   uint2* srect;           // [n] out
   uint32_t* offsets;      // [n] out: exclusive scan of wsrc in sorted order
@@ -424,6 +424,14 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
     grid.sync();
   }
   // tail: srect[i] = rect[sorted[i]]; offsets = exclusive scan of wsrc[sorted[i]]
+  if (!a.wsrc) {   // band binning needs the depth-ordered rects only
+#pragma unroll
+    for (int q = 0; q < kSortIpt; ++q) {
+      const uint32_t i = blk * kSortChunk + q * kSortThreads + threadIdx.x;
+      if (i < n) a.srect[i] = a.rect[__ldcg(a.valB + i)];
+    }
+    return;
+  }
   const uint32_t tbase = blk * kSortChunk + threadIdx.x * kSortIpt;
   uint32_t pre[kSortIpt];
   uint32_t s = 0;
