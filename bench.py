@@ -567,7 +567,7 @@ C3 = dict(P=1_000_000, W=1920, H=1080, seed=1)
 
 
 def surfel_leg(args, local) -> dict:
-    from pings_b200 import synth
+    from pings_b200 import _lib as L, synth
     from pings_b200.diff_gaussian_surfel_rasterization import GaussianRasterizationSettings, GaussianRasterizer
     from pings_b200.fused_ssim import fused_ssim
     dev = torch.device("cuda", local)
@@ -620,6 +620,16 @@ def surfel_leg(args, local) -> dict:
         evs.append((a, b))
     torch.cuda.synchronize()
     ms = sum(a.elapsed_time(b) for a, b in evs) / steps
+    # per-phase device time of the library kernels inside the step (the rest is the SSIM kernels + torch loss glue)
+    c3_phases: dict[str, list[float]] = {}
+    L.timing_enable(True)
+    for _ in range(3):
+        flush.fill_(1)
+        step()
+        for name, pms in L.timing_drain():
+            c3_phases.setdefault(name, []).append(pms)
+    L.timing_enable(False)
+    c3_phase_ms = {k: round(sum(v) / len(v), 4) for k, v in c3_phases.items()}
     # standalone fused SSIM fwd+bwd on [1,3,1080,1920] (24 + 28 B/element algorithmic)
     img = torch.rand(1, 3, H, W, device=dev, requires_grad=True)
     tgt = target.unsqueeze(0)
@@ -639,6 +649,7 @@ def surfel_leg(args, local) -> dict:
     return {"surfel_ssim": {"metric": "surfel raster fwd+bwd Mpix/s (RGB+depth+normal, fused-SSIM loss, C3)",
                             "value": round(W * H / (ms * 1e-3) / 1e6, 2), "unit": "Mpix/s", "ms_per_step": round(ms, 4),
                             "P": P, "W": W, "H": H, "visible": int((info["vis"] > 0).sum()),
+                            "phases_ms": c3_phase_ms,
                             "note": "through GaussianRasterizer + fused_ssim autograd modules, loss and torch glue included",
                             "ssim_fwd_bwd": {"ms": round(ssim_ms, 4), "gbs": round(ssim_gbs, 1),
                                              "frac": round(ssim_gbs / pk["hbm_gbs"], 4), "alg_bytes_per_elem": 52}}}

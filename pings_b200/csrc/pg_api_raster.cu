@@ -1,4 +1,5 @@
 // C-ABI entry points of the rasterizer (see include/pings_b200.h).
+#include <cstdlib>
 #include "pg_rasters_bwd.cuh"
 
 namespace pg {
@@ -198,12 +199,20 @@ int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g, void* ge
   if (num_rendered > 0) {
     const uint32_t* point_list = sorted_point_list(bw, W, H);
     Phase ph("render_bwd", st);
-    if (surfel)
-      rs_render_bwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, gw.ext, gw.zyv,
-                                                          prm->bg, prm->config, iw.final_T, iw.final_D, iw.n_contrib,
-                                                          in->dL_dout_color, in->dL_dout_normal, in->dL_dout_depth,
-                                                          in->dL_dout_opac, gw.gacc);
-    else
+    if (surfel) {
+      // 4 warps x pixel pairs by default; PG_RS_BWD_WARPS=2 selects the 2 warps x quads layout (dev A/B knob)
+      static const int nw = [] { const char* e = getenv("PG_RS_BWD_WARPS"); return (e && atoi(e) == 2) ? 2 : 4; }();
+      if (nw == 4)
+        rs_render_bwd_kernel<4><<<gx * gy, 128, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, gw.ext, gw.zyv,
+                                                         prm->bg, prm->config, iw.final_T, iw.final_D, iw.n_contrib,
+                                                         in->dL_dout_color, in->dL_dout_normal, in->dL_dout_depth,
+                                                         in->dL_dout_opac, gw.gacc);
+      else
+        rs_render_bwd_kernel<2><<<gx * gy, 64, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, gw.ext, gw.zyv,
+                                                        prm->bg, prm->config, iw.final_T, iw.final_D, iw.n_contrib,
+                                                        in->dL_dout_color, in->dL_dout_normal, in->dL_dout_depth,
+                                                        in->dL_dout_opac, gw.gacc);
+    } else
       r3_render_bwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
                                                           iw.final_T, iw.n_contrib, in->dL_dout_color,
                                                           in->dL_dout_depth, gw.gacc);

@@ -47,11 +47,12 @@ __device__ __forceinline__ void warp_reduce16_store(float (&v)[16], int lane, fl
   if (!(lane & 1)) dst[index] = v[0];
 }
 
+template <int NW>
 struct RSBwdSlab {
   RSSlab in;
-  float acc[2][kRBatch][16];  // per-warp partial sums of the current batch
-  uint32_t flag[2][kRBatch];
-  uint32_t wmax[2];
+  float acc[NW][kRBatch][16];  // per-warp partial sums of the current batch
+  uint32_t flag[NW][kRBatch];
+  uint32_t wmax[NW];
 };
 
 // Gradient accumulation record per surfel (4 x float4):
@@ -61,33 +62,41 @@ struct RSBwdSlab {
 //   gacc[4i+3] = (dL_dnormal.x, .y, .z, 0)      (already x10, RS backward.cu:783)
 // The per-pixel-depth term of dL_dmean2D (RS backward.cu:894-897) is -S * (zx, zy): it does not
 // depend on the pixel, so it is applied once per surfel in the per-surfel kernel.
-__global__ void __launch_bounds__(kRThreads) rs_render_bwd_kernel(
+// NW warps per 16x16 tile: a warp owns a 16 x (16/NW) strip and a lane 8/NW pixels of it (2x2 quad for
+// NW = 2, 2x1 pair for NW = 4).  The surfel backward keeps ~36 floats of state per pixel, so the quad
+// layout needs 205 registers (4 CTAs = 8 warps per SM); pairs halve the per-thread state and double the
+// resident warps at the price of one more partial-sum reduction per (warp, surfel).
+template <int NW>
+__global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int gx,
     const float4* __restrict__ rec, const float4* __restrict__ ext, const float* __restrict__ zyv,
     const float* __restrict__ bg, const float* __restrict__ config, const float* __restrict__ final_T,
     const float* __restrict__ final_D, const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
     const float* __restrict__ dL_dpix_normal, const float* __restrict__ dL_dpix_depth,
     const float* __restrict__ dL_dpix_opac, float4* __restrict__ gacc) {
-  __shared__ RSBwdSlab sm;
+  constexpr int PX = 8 / NW;          // pixels per lane
+  constexpr int RH = kTile / NW;      // rows per warp
+  static_assert(NW == 2 || NW == 4, "2 or 4 warps per tile");
+  __shared__ RSBwdSlab<NW> sm;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tile = blockIdx.x;
   const int tx = tile % gx, ty = tile / gx;
-  const int rx0 = tx * kTile, ry0 = ty * kTile + warp * 8;
-  const int qx = rx0 + (lane & 7) * 2, qy = ry0 + (lane >> 3) * 2;
+  const int rx0 = tx * kTile, ry0 = ty * kTile + warp * RH;
+  const int qx = rx0 + (lane & 7) * 2, qy = ry0 + (lane >> 3) * (PX / 2);
   const float fxs[2] = {(float)qx, (float)(qx + 1)};
   const float fys[2] = {(float)qy, (float)(qy + 1)};
   const float wx0 = (float)rx0, wx1 = (float)min(rx0 + 15, W - 1);
-  const float wy0 = (float)ry0, wy1 = (float)min(ry0 + 7, H - 1);
+  const float wy0 = (float)ry0, wy1 = (float)min(ry0 + RH - 1, H - 1);
   const size_t HW = (size_t)H * W;
   const bool surface = config[0] > 0, normalize_depth = config[1] > 0, ppd = surface && (config[2] > 0);
 
-  float T[4], Tfin[4], Dfin[4], acr[4][3], acn[4][3], acd[4], lalpha[4], lcol[4][3], lnrm[4][3], ldep[4];
-  float dpx[4][3], dpn[4][3], dpd[4], dpo[4], bgdot[4];
-  uint32_t lastc[4];
+  float T[PX], Tfin[PX], Dfin[PX], acr[PX][3], acn[PX][3], acd[PX], lalpha[PX], lcol[PX][3], lnrm[PX][3], ldep[PX];
+  float dpx[PX][3], dpn[PX][3], dpd[PX], dpo[PX], bgdot[PX];
+  uint32_t lastc[PX];
   const float b0 = bg[0], b1 = bg[1], b2 = bg[2];
   uint32_t my_max = 0;
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
+  for (int k = 0; k < PX; ++k) {
     const int x = qx + (k & 1), y = qy + (k >> 1);
     const bool in = x < W && y < H;
     const size_t pix = (size_t)W * y + x;
@@ -110,26 +119,31 @@ __global__ void __launch_bounds__(kRThreads) rs_render_bwd_kernel(
   }
   const uint32_t wmax = __reduce_max_sync(0xffffffffu, my_max);
   if (lane == 0) sm.wmax[warp] = wmax;
-  sm.flag[0][tid] = 0;
-  sm.flag[1][tid] = 0;
+  if (tid < kRBatch) {
+#pragma unroll
+    for (int w = 0; w < NW; ++w) sm.flag[w][tid] = 0;
+  }
   __syncthreads();
   const uint2 range = ranges[tile];
-  const int n_eff = (int)min(max(sm.wmax[0], sm.wmax[1]), range.y - range.x);
+  uint32_t tmax = sm.wmax[0];
+#pragma unroll
+  for (int w = 1; w < NW; ++w) tmax = max(tmax, sm.wmax[w]);
+  const int n_eff = (int)min(tmax, range.y - range.x);
   const int rounds = (n_eff + kRBatch - 1) / kRBatch;
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
-  if (tid < n_eff) rs_stage(sm.in, 0, tid, point_list[range.x + (n_eff - 1 - tid)], rec, ext, zyv);
+  if (tid < kRBatch && tid < n_eff) rs_stage(sm.in, 0, tid, point_list[range.x + (n_eff - 1 - tid)], rec, ext, zyv);
   cp_async_commit();
   uint32_t nxt = 0;
-  if (kRBatch + tid < n_eff) nxt = point_list[range.x + (n_eff - 1 - kRBatch - tid)];
+  if (tid < kRBatch && kRBatch + tid < n_eff) nxt = point_list[range.x + (n_eff - 1 - kRBatch - tid)];
 
   int cur = 0;
   for (int r = 0; r < rounds; ++r) {
     cp_async_wait_all();
     __syncthreads();
-    if ((r + 1) * kRBatch + tid < n_eff) rs_stage(sm.in, cur ^ 1, tid, nxt, rec, ext, zyv);
+    if (tid < kRBatch && (r + 1) * kRBatch + tid < n_eff) rs_stage(sm.in, cur ^ 1, tid, nxt, rec, ext, zyv);
     cp_async_commit();
-    if ((r + 2) * kRBatch + tid < n_eff) nxt = point_list[range.x + (n_eff - 1 - (r + 2) * kRBatch - tid)];
+    if (tid < kRBatch && (r + 2) * kRBatch + tid < n_eff) nxt = point_list[range.x + (n_eff - 1 - (r + 2) * kRBatch - tid)];
 
     const int cnt = min(kRBatch, n_eff - r * kRBatch);
 #pragma unroll 1
@@ -149,11 +163,11 @@ __global__ void __launch_bounds__(kRThreads) rs_render_bwd_kernel(
         const uint32_t pos = (uint32_t)(n_eff - 1 - (r * kRBatch + j));
         const float4 e = sm.in.a[cur][j];
         const float4 co = sm.in.b[cur][j];
-        float G[4], al[4], ddx[4], ddy[4];
-        bool act[4];
+        float G[PX], al[PX], ddx[PX], ddy[PX];
+        bool act[PX];
         bool any = false;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
+        for (int k = 0; k < PX; ++k) {
           ddx[k] = e.x - fxs[k & 1];
           ddy[k] = e.y - fys[k >> 1];
           const float dist = (co.x * ddx[k] * ddx[k] + co.z * ddy[k] * ddy[k]) + 2 * co.y * ddx[k] * ddy[k];
@@ -174,7 +188,7 @@ __global__ void __launch_bounds__(kRThreads) rs_render_bwd_kernel(
           const float col[3] = {cd.y, cd.z, cd.w};
           const float nrm[3] = {ne.x, ne.y, ne.z};
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
+          for (int k = 0; k < PX; ++k) {
             if (act[k]) {
               const float alpha = al[k];
               const float inv1ma = __frcp_rn(1.f - alpha);   // shared by the divisions of RS backward.cu (see R3 kernel)
@@ -231,19 +245,35 @@ __global__ void __launch_bounds__(kRThreads) rs_render_bwd_kernel(
       }
     }
     __syncthreads();
-    {
-      const uint32_t f0 = sm.flag[0][tid], f1 = sm.flag[1][tid];
-      if (f0 | f1) {
+    if (tid < kRBatch) {
+      uint32_t f[NW], fany = 0;
+#pragma unroll
+      for (int w = 0; w < NW; ++w) {
+        f[w] = sm.flag[w][tid];
+        fany |= f[w];
+      }
+      if (fany) {
         float s[16];
 #pragma unroll
-        for (int q = 0; q < 16; ++q) s[q] = (f0 ? sm.acc[0][tid][q] : 0.f) + (f1 ? sm.acc[1][tid][q] : 0.f);
+        for (int q = 0; q < 16; ++q) s[q] = 0.f;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) {
+          if (f[w]) {
+            const float4* ap = reinterpret_cast<const float4*>(&sm.acc[w][tid][0]);
+#pragma unroll
+            for (int q4 = 0; q4 < 4; ++q4) {
+              const float4 t = ap[q4];
+              s[4 * q4 + 0] += t.x; s[4 * q4 + 1] += t.y; s[4 * q4 + 2] += t.z; s[4 * q4 + 3] += t.w;
+            }
+          }
+        }
         float4* dst = gacc + 4 * (size_t)sm.in.id[cur][tid];
         atomicAdd(dst + 0, make_float4(s[0], s[1], s[2], s[3]));
         atomicAdd(dst + 1, make_float4(s[4], s[5], s[6], s[7]));
         atomicAdd(dst + 2, make_float4(s[8], s[9], s[10], 0.f));
         if (surface) atomicAdd(dst + 3, make_float4(s[11], s[12], s[13], 0.f));
-        sm.flag[0][tid] = 0;
-        sm.flag[1][tid] = 0;
+#pragma unroll
+        for (int w = 0; w < NW; ++w) sm.flag[w][tid] = 0;
       }
     }
     cur ^= 1;
