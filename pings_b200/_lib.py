@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpings_b200.so")
+LIB_PATH = os.environ.get("PINGS_B200_LIB") or os.path.join(_HERE, "libpings_b200.so")   # env override: dev A/B of two builds
 
 PG_OK = 0
 PG_VARIANT_3DGS = 0

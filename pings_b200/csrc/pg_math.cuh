@@ -78,4 +78,13 @@ __host__ __device__ __forceinline__ void tile_rect(float px, float py, int radiu
   y1 = clampi((int)((py + radius + 16 - 1) / 16), gy);
 }
 
+// Reciprocal for normal-range arguments: MUFU.RCP + one Newton step (3 instructions, no slow-path branch;
+// <= 1 ulp).  __frcp_rn / IEEE division cost ~10 instructions and a divergent call each in the blend loops.
+__device__ __forceinline__ float rcp_nr(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  const float e = fmaf(-x, r, 1.0f);
+  return fmaf(r, e, r);
+}
+
 }  // namespace pg

@@ -184,9 +184,9 @@ __global__ void __launch_bounds__(kRThreads) r3_render_bwd_kernel(
           for (int k = 0; k < 4; ++k) {
             if (act[k]) {
               const float alpha = al[k];
-              // one correctly rounded reciprocal serves both divisions by (1 - alpha) of R3 backward.cu:672,719
-              // (<= 1 ulp from the quotients; far inside the gradient tolerance)
-              const float inv1ma = __frcp_rn(1.f - alpha);
+              // one reciprocal serves both divisions by (1 - alpha) of R3 backward.cu:672,719
+              // (<= 1.5 ulp from the quotients; far inside the gradient tolerance)
+              const float inv1ma = rcp_nr(1.f - alpha);
               T[k] = T[k] * inv1ma;
               const float dchannel_dcolor = alpha * T[k];
               float dL_dalpha = 0.0f;
@@ -204,15 +204,15 @@ __global__ void __launch_bounds__(kRThreads) r3_render_bwd_kernel(
               dL_dalpha *= T[k];
               lalpha[k] = alpha;
               dL_dalpha += (-Tfin[k] * inv1ma) * bgdot[k];
+              // v[0..4] are accumulated without their constant factors (-ddelx_dx, -ddely_dy, -0.5), which the
+              // flush applies once per staged Gaussian instead of once per pixel pair.
               const float dL_dG = co.w * dL_dalpha;
-              const float gdx = G[k] * ddx[k], gdy = G[k] * ddy[k];
-              const float dG_ddelx = -gdx * co.x - gdy * co.y;
-              const float dG_ddely = -gdy * co.z - gdx * co.y;
-              v[0] += dL_dG * dG_ddelx * ddelx_dx;
-              v[1] += dL_dG * dG_ddely * ddely_dy;
-              v[2] += -0.5f * gdx * ddx[k] * dL_dG;
-              v[3] += -0.5f * gdx * ddy[k] * dL_dG;
-              v[4] += -0.5f * gdy * ddy[k] * dL_dG;
+              const float hx = dL_dG * (G[k] * ddx[k]), hy = dL_dG * (G[k] * ddy[k]);
+              v[0] = fmaf(hy, co.y, fmaf(hx, co.x, v[0]));
+              v[1] = fmaf(hx, co.y, fmaf(hy, co.z, v[1]));
+              v[2] = fmaf(hx, ddx[k], v[2]);
+              v[3] = fmaf(hx, ddy[k], v[3]);
+              v[4] = fmaf(hy, ddy[k], v[4]);
               v[5] += G[k] * dL_dalpha;
             }
           }
@@ -230,8 +230,8 @@ __global__ void __launch_bounds__(kRThreads) r3_render_bwd_kernel(
 #pragma unroll
         for (int q = 0; q < 12; ++q) s[q] = (f0 ? sm.acc[0][tid][q] : 0.f) + (f1 ? sm.acc[1][tid][q] : 0.f);
         float4* dst = gacc + 3 * (size_t)sm.id[cur][tid];
-        atomicAdd(dst + 0, make_float4(s[0], s[1], s[2], s[3]));
-        atomicAdd(dst + 1, make_float4(s[4], s[5], s[6], 0.f));
+        atomicAdd(dst + 0, make_float4(-ddelx_dx * s[0], -ddely_dy * s[1], -0.5f * s[2], -0.5f * s[3]));
+        atomicAdd(dst + 1, make_float4(-0.5f * s[4], s[5], s[6], 0.f));
         atomicAdd(dst + 2, make_float4(s[8], s[9], s[10], 0.f));
         sm.flag[0][tid] = 0;
         sm.flag[1][tid] = 0;

@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
   const bool surface = config[0] > 0, normalize_depth = config[1] > 0, ppd = surface && (config[2] > 0);
 
   float T[PX], Tfin[PX], Dfin[PX], acr[PX][3], acn[PX][3], acd[PX], lalpha[PX], lcol[PX][3], lnrm[PX][3], ldep[PX];
-  float dpx[PX][3], dpn[PX][3], dpd[PX], dpo[PX], bgdot[PX];
+  float dpx[PX][3], dpn[PX][3], dpd[PX], dpo[PX], bgdot[PX], dLc[PX], cN[PX], dpoT[PX], bgx[PX];
   uint32_t lastc[PX];
   const float b0 = bg[0], b1 = bg[1], b2 = bg[2];
   uint32_t my_max = 0;
@@ -116,6 +116,14 @@ __global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
     dpo[k] = in ? dL_dpix_opac[pix] : 0.f;
     acd[k] = 0.f; lalpha[k] = 0.f; ldep[k] = 0.f;
     bgdot[k] = b0 * dpx[k][0] + b1 * dpx[k][1] + b2 * dpx[k][2];
+    // Per-pixel constants of RS backward.cu:822-870 hoisted out of the list walk (same operand order as the
+    // reference's in-loop expressions, so the hoisted parts are bit-identical): the walk keeps no IEEE division.
+    const float omT = 1.f - Tfin[k];   // >= 1e-6 for in-image pixels (RS forward.cu:608 clamps T_final)
+    const bool nd = normalize_depth && in;
+    dLc[k] = nd ? dpd[k] / omT : dpd[k];
+    cN[k] = nd ? dpd[k] * Dfin[k] / omT / omT * -Tfin[k] : 0.f;
+    dpoT[k] = dpo[k] * Tfin[k];
+    bgx[k] = normalize_depth ? bgdot[k] : bgdot[k] + 10 * dpd[k];
   }
   const uint32_t wmax = __reduce_max_sync(0xffffffffu, my_max);
   if (lane == 0) sm.wmax[warp] = wmax;
@@ -191,7 +199,7 @@ __global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
           for (int k = 0; k < PX; ++k) {
             if (act[k]) {
               const float alpha = al[k];
-              const float inv1ma = __frcp_rn(1.f - alpha);   // shared by the divisions of RS backward.cu (see R3 kernel)
+              const float inv1ma = rcp_nr(1.f - alpha);   // serves every division by (1 - alpha) (see the R3 kernel)
               T[k] = T[k] * inv1ma;
               const float dchannel_dcolor = alpha * T[k];
               float dL_dalpha = 0.0f;
@@ -215,26 +223,26 @@ __global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
                 const float d_cur = cd.x - (ddx[k] * ne.w + ddy[k] * zyj);
                 acd[k] = lalpha[k] * ldep[k] + (1.f - lalpha[k]) * acd[k];
                 ldep[k] = d_cur;
-                float dL_dchannel = dpd[k], dL_dalpha_depth = 0.f;
-                if (normalize_depth) {
-                  dL_dchannel /= (1.f - Tfin[k]);
-                  dL_dalpha_depth += dpd[k] * Dfin[k] / (1.f - Tfin[k]) / (1.f - Tfin[k]) * -Tfin[k] / (1 - alpha) / T[k];
-                }
-                dL_dalpha_depth += (d_cur - acd[k]) * dL_dchannel;
-                v[6] += dchannel_dcolor * dL_dchannel * 1;
+                // RS backward.cu:842-850: dpd*D/(1-Tf)^2 * -Tf / (1-alpha) / T, the first four factors hoisted (cN)
+                float dL_dalpha_depth = normalize_depth ? cN[k] * inv1ma * rcp_nr(T[k]) : 0.f;
+                dL_dalpha_depth += (d_cur - acd[k]) * dLc[k];
+                v[6] += dchannel_dcolor * dLc[k];
                 dL_dalpha += dL_dalpha_depth;
               }
               dL_dalpha *= T[k];
-              dL_dalpha += dpo[k] * Tfin[k] / (1 - alpha);
+              dL_dalpha += dpoT[k] * inv1ma;
               lalpha[k] = alpha;
-              dL_dalpha += (-Tfin[k] * inv1ma) * bgdot[k];
-              if (!normalize_depth) dL_dalpha += (-Tfin[k] * inv1ma) * (10 * dpd[k]);
-              const float dL_ddist = dL_dalpha * co.w * -0.5f * G[k];
-              v[0] += dL_ddist * 2 * (co.x * ddx[k] + co.y * ddy[k]) * ddelx_dx;
-              v[1] += dL_ddist * 2 * (co.z * ddy[k] + co.y * ddx[k]) * ddely_dy;
-              v[2] += dL_ddist * (ddx[k] * ddx[k]);
-              v[3] += dL_ddist * (1 * ddx[k] * ddy[k]);
-              v[4] += dL_ddist * (ddy[k] * ddy[k]);
+              // background colour term, plus the +10*T depth padding when depth is not normalised (bgx)
+              dL_dalpha += (-Tfin[k] * inv1ma) * bgx[k];
+              // dL_ddist = -0.5 * g; v[0..4] are accumulated without their constant factors (-ddelx_dx, -ddely_dy,
+              // -0.5), which the flush applies once per staged surfel (RS backward.cu:872-880).
+              const float g = (dL_dalpha * co.w) * G[k];
+              const float hx = g * ddx[k], hy = g * ddy[k];
+              v[0] = fmaf(hy, co.y, fmaf(hx, co.x, v[0]));
+              v[1] = fmaf(hx, co.y, fmaf(hy, co.z, v[1]));
+              v[2] = fmaf(hx, ddx[k], v[2]);
+              v[3] = fmaf(hx, ddy[k], v[3]);
+              v[4] = fmaf(hy, ddy[k], v[4]);
               v[5] += G[k] * dL_dalpha;
               if (ppd) v[7] += dpd[k];
             }
@@ -268,8 +276,8 @@ __global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
           }
         }
         float4* dst = gacc + 4 * (size_t)sm.in.id[cur][tid];
-        atomicAdd(dst + 0, make_float4(s[0], s[1], s[2], s[3]));
-        atomicAdd(dst + 1, make_float4(s[4], s[5], s[6], s[7]));
+        atomicAdd(dst + 0, make_float4(-ddelx_dx * s[0], -ddely_dy * s[1], -0.5f * s[2], -0.5f * s[3]));
+        atomicAdd(dst + 1, make_float4(-0.5f * s[4], s[5], s[6], s[7]));
         atomicAdd(dst + 2, make_float4(s[8], s[9], s[10], 0.f));
         if (surface) atomicAdd(dst + 3, make_float4(s[11], s[12], s[13], 0.f));
 #pragma unroll

@@ -93,9 +93,12 @@ def test_forward_bitexact_and_backward(P, W, H, seed, cfg):
     # up to 4e-2 of the tensor max between runs (tools/dev_check_rasters.py), so those tensors are held
     # to: >= 99 % of the visible rows within 1e-2 relative (row-wise, floor 1e-3 of the tensor max),
     # and no row off by more than max(5 %, 10x the reference's own spread) of the tensor max.
+    # The spread is taken over 6 reference runs: with 3 it came out anywhere between 0.3 % and 3 % of
+    # the tensor max on the same scene (tools/dev_surfel_grad_spread.py: ref-ref 2-3 %, ours-ours 0.01 %,
+    # ours-ref 8-12 % on the single worst row of `scales`), which made the bar itself a coin toss.
     runs = [g] + [ref.backward(sc, (view, full, proj), cam.tanfovx, cam.tanfovy, bg, ex["prcppoint"], ex["patch_bbox"],
                                config, r["radii"], ct["color"], ct["normal"], ct["depth"], ct["opac"], campos=center)
-                  for _ in range(2)]
+                  for _ in range(5)]
     names = ["means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations", "tau"]
     nvis = int((radii > 0).sum())
     for n, t in zip(names, out):
