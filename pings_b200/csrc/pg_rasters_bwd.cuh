@@ -180,7 +180,10 @@ __global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
           ddy[k] = e.y - fys[k >> 1];
           const float dist = (co.x * ddx[k] * ddx[k] + co.z * ddy[k] * ddy[k]) + 2 * co.y * ddx[k] * ddy[k];
           const float power = -0.5f * dist;
-          G[k] = expf(power);
+          // ex2.approx(power * log2e): ~5 ulp on power in [-5.5, 0] (2 instructions instead of expf's 8).  The forward
+          // keeps the accurate expf because n_contrib / the alpha >= 1/255 decisions are compared bit for bit; here a
+          // decision can only differ for alpha within a few ulp of 1/255, a <= 0.4 % change of one pixel's terms.
+          G[k] = __expf(power);
           al[k] = fminf(0.99f, co.w * G[k]);
           act[k] = (pos < lastc[k]) && !(power > 0.0f) && !(al[k] < 1.0f / 255.0f);
           any |= act[k];
