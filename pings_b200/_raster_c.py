@@ -86,10 +86,13 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     dev = means3D.device
     P, H, W = means3D.size(0), int(image_height), int(image_width)
     fopt = dict(dtype=torch.float32, device=dev)
-    out_color = torch.zeros(3, H, W, **fopt)
-    out_depth = torch.zeros(1, H, W, **fopt)
-    out_opacity = torch.zeros(1, H, W, **fopt)
-    radii = torch.zeros(P, dtype=torch.int32, device=dev)
+    # With P > 0 the kernels write every pixel and every radii entry, so only the accumulated outputs are
+    # zero-filled (each fill is one more launch per step); P == 0 returns zeros like the reference.
+    alloc = torch.empty if P != 0 else torch.zeros
+    out_color = alloc(3, H, W, **fopt)
+    out_depth = alloc(1, H, W, **fopt)
+    out_opacity = alloc(1, H, W, **fopt)
+    radii = alloc(P, dtype=torch.int32, device=dev)
     n_touched = torch.zeros(P, dtype=torch.int32, device=dev)
     bopt = dict(dtype=torch.uint8, device=dev)
     geom = torch.empty(0, **bopt)
@@ -199,11 +202,12 @@ def rasterize_gaussians_surfel(background, means3D, colors, opacity, scales, rot
     dev = means3D.device
     P, H, W = means3D.size(0), int(image_height), int(image_width)
     fopt = dict(dtype=torch.float32, device=dev)
-    out_color = torch.zeros(3, H, W, **fopt)
-    out_normal = torch.zeros(3, H, W, **fopt)
-    out_depth = torch.zeros(1, H, W, **fopt)
-    out_opac = torch.zeros(1, H, W, **fopt)
-    radii = torch.zeros(P, dtype=torch.int32, device=dev)
+    alloc = torch.empty if P != 0 else torch.zeros   # see rasterize_gaussians
+    out_color = alloc(3, H, W, **fopt)
+    out_normal = alloc(3, H, W, **fopt)
+    out_depth = alloc(1, H, W, **fopt)
+    out_opac = alloc(1, H, W, **fopt)
+    radii = alloc(P, dtype=torch.int32, device=dev)
     contributions = torch.zeros(P, **fopt)
     bopt = dict(dtype=torch.uint8, device=dev)
     geom = torch.empty(0, **bopt)
