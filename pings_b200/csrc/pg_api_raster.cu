@@ -200,8 +200,9 @@ int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g, void* ge
     const uint32_t* point_list = sorted_point_list(bw, W, H);
     Phase ph("render_bwd", st);
     if (surfel) {
-      // 4 warps x pixel pairs by default; PG_RS_BWD_WARPS=2 selects the 2 warps x quads layout (dev A/B knob)
-      static const int nw = [] { const char* e = getenv("PG_RS_BWD_WARPS"); return (e && atoi(e) == 2) ? 2 : 4; }();
+      // 2 warps x quads by default (fewest per-surfel reductions; 882 vs 971 us at C3 once the accum_rec state
+      // became two scalars per pixel); PG_RS_BWD_WARPS=4 selects 4 warps x pixel pairs (dev A/B knob)
+      static const int nw = [] { const char* e = getenv("PG_RS_BWD_WARPS"); return (e && atoi(e) == 4) ? 4 : 2; }();
       if (nw == 4)
         rs_render_bwd_kernel<4><<<gx * gy, 128, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, gw.ext, gw.zyv,
                                                          prm->bg, prm->config, iw.final_T, iw.final_D, iw.n_contrib,

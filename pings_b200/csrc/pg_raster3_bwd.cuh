@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(kRThreads) r3_render_bwd_kernel(
   const float wy0 = (float)ry0, wy1 = (float)min(ry0 + 7, H - 1);
   const size_t HW = (size_t)H * W;
 
-  float T[4], Tfin[4], acr[4][3], acd[4], lalpha[4], lcol[4][3], ldep[4], dpx[4][3], dpd[4], bgdot[4];
+  float T[4], Tfin[4], accA[4], lastB[4], lalpha[4], dpx[4][3], dpd[4], bgdot[4];
   uint32_t lastc[4];
   const float b0 = bg[0], b1 = bg[1], b2 = bg[2];
   uint32_t my_max = 0;
@@ -99,11 +99,9 @@ __global__ void __launch_bounds__(kRThreads) r3_render_bwd_kernel(
 #pragma unroll
     for (int ch = 0; ch < 3; ++ch) {
       dpx[k][ch] = in ? dL_dpix[ch * HW + pix] : 0.f;
-      acr[k][ch] = 0.f;
-      lcol[k][ch] = 0.f;
     }
     dpd[k] = in ? dL_dpix_depth[pix] : 0.f;
-    acd[k] = 0.f; lalpha[k] = 0.f; ldep[k] = 0.f;
+    accA[k] = 0.f; lastB[k] = 0.f; lalpha[k] = 0.f;
     bgdot[k] = b0 * dpx[k][0] + b1 * dpx[k][1] + b2 * dpx[k][2];
   }
   const uint32_t wmax = __reduce_max_sync(0xffffffffu, my_max);
@@ -192,19 +190,17 @@ __global__ void __launch_bounds__(kRThreads) r3_render_bwd_kernel(
               const float inv1ma = rcp_nr(1.f - alpha);
               T[k] = T[k] * inv1ma;
               const float dchannel_dcolor = alpha * T[k];
-              float dL_dalpha = 0.0f;
+              // R3 backward.cu:683-716 keeps, per channel, the colour accumulated behind this Gaussian (accum_rec)
+              // and adds (c_ch - accum_rec_ch) * dL_dpixel_ch to dL_dalpha.  Only the dot product with the pixel
+              // cotangent is ever used, and the recurrence is linear, so one scalar per pixel carries it:
+              // A <- lalpha * B_last + (1 - lalpha) * A with B = sum_ch c_ch * dL_dpixel_ch (depth is a 4th channel).
+              const float B = fmaf(cd.x, dpd[k], fmaf(col[2], dpx[k][2], fmaf(col[1], dpx[k][1], col[0] * dpx[k][0])));
+              accA[k] = fmaf(lalpha[k], lastB[k] - accA[k], accA[k]);
+              lastB[k] = B;
 #pragma unroll
-              for (int ch = 0; ch < 3; ++ch) {
-                acr[k][ch] = lalpha[k] * lcol[k][ch] + (1.f - lalpha[k]) * acr[k][ch];
-                lcol[k][ch] = col[ch];
-                dL_dalpha += (col[ch] - acr[k][ch]) * dpx[k][ch];
-                v[8 + ch] += dchannel_dcolor * dpx[k][ch];
-              }
-              acd[k] = lalpha[k] * ldep[k] + (1.f - lalpha[k]) * acd[k];
-              ldep[k] = cd.x;
-              dL_dalpha += (cd.x - acd[k]) * dpd[k];
+              for (int ch = 0; ch < 3; ++ch) v[8 + ch] += dchannel_dcolor * dpx[k][ch];
               v[6] += dchannel_dcolor * dpd[k];
-              dL_dalpha *= T[k];
+              float dL_dalpha = (B - accA[k]) * T[k];
               lalpha[k] = alpha;
               dL_dalpha += (-Tfin[k] * inv1ma) * bgdot[k];
               // v[0..4] are accumulated without their constant factors (-ddelx_dx, -ddely_dy, -0.5), which the

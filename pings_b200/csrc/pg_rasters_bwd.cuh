@@ -67,7 +67,7 @@ struct RSBwdSlab {
 // layout needs 205 registers (4 CTAs = 8 warps per SM); pairs halve the per-thread state and double the
 // resident warps at the price of one more partial-sum reduction per (warp, surfel).
 template <int NW>
-__global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
+__global__ void __launch_bounds__(NW * 32, NW == 2 ? 8 : 5) rs_render_bwd_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int gx,
     const float4* __restrict__ rec, const float4* __restrict__ ext, const float* __restrict__ zyv,
     const float* __restrict__ bg, const float* __restrict__ config, const float* __restrict__ final_T,
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
   const size_t HW = (size_t)H * W;
   const bool surface = config[0] > 0, normalize_depth = config[1] > 0, ppd = surface && (config[2] > 0);
 
-  float T[PX], Tfin[PX], Dfin[PX], acr[PX][3], acn[PX][3], acd[PX], lalpha[PX], lcol[PX][3], lnrm[PX][3], ldep[PX];
+  float T[PX], Tfin[PX], Dfin[PX], accA[PX], lastB[PX], lalpha[PX];
   float dpx[PX][3], dpn[PX][3], dpd[PX], dpo[PX], bgdot[PX], dLc[PX], cN[PX], dpoT[PX], bgx[PX];
   uint32_t lastc[PX];
   const float b0 = bg[0], b1 = bg[1], b2 = bg[2];
@@ -109,12 +109,10 @@ __global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
     for (int ch = 0; ch < 3; ++ch) {
       dpx[k][ch] = in ? dL_dpix[ch * HW + pix] : 0.f;
       dpn[k][ch] = in ? dL_dpix_normal[ch * HW + pix] : 0.f;
-      acr[k][ch] = acn[k][ch] = 0.f;
-      lcol[k][ch] = lnrm[k][ch] = 0.f;
     }
     dpd[k] = in ? dL_dpix_depth[pix] : 0.f;
     dpo[k] = in ? dL_dpix_opac[pix] : 0.f;
-    acd[k] = 0.f; lalpha[k] = 0.f; ldep[k] = 0.f;
+    accA[k] = 0.f; lastB[k] = 0.f; lalpha[k] = 0.f;
     bgdot[k] = b0 * dpx[k][0] + b1 * dpx[k][1] + b2 * dpx[k][2];
     // Per-pixel constants of RS backward.cu:822-870 hoisted out of the list walk (same operand order as the
     // reference's in-loop expressions, so the hoisted parts are bit-identical): the walk keeps no IEEE division.
@@ -205,33 +203,24 @@ __global__ void __launch_bounds__(NW * 32) rs_render_bwd_kernel(
               const float inv1ma = rcp_nr(1.f - alpha);   // serves every division by (1 - alpha) (see the R3 kernel)
               T[k] = T[k] * inv1ma;
               const float dchannel_dcolor = alpha * T[k];
-              float dL_dalpha = 0.0f;
+              // Scalar form of the accum_rec recurrences of RS backward.cu:797-850 (see the R3 kernel): colour,
+              // normal and depth are 7 channels of one dot product with the pixel cotangents.
+              const float d_cur = cd.x - (ddx[k] * ne.w + ddy[k] * zyj);
+              float B = fmaf(d_cur, dLc[k], fmaf(col[2], dpx[k][2], fmaf(col[1], dpx[k][1], col[0] * dpx[k][0])));
 #pragma unroll
-              for (int ch = 0; ch < 3; ++ch) {
-                acr[k][ch] = lalpha[k] * lcol[k][ch] + (1.f - lalpha[k]) * acr[k][ch];
-                lcol[k][ch] = col[ch];
-                dL_dalpha += (col[ch] - acr[k][ch]) * dpx[k][ch];
-                v[8 + ch] += dchannel_dcolor * dpx[k][ch];
-              }
+              for (int ch = 0; ch < 3; ++ch) v[8 + ch] += dchannel_dcolor * dpx[k][ch];
               if (surface) {
+                B = fmaf(nrm[2], dpn[k][2], fmaf(nrm[1], dpn[k][1], fmaf(nrm[0], dpn[k][0], B)));
+                const float dcn = dchannel_dcolor * 10;
 #pragma unroll
-                for (int ch = 0; ch < 3; ++ch) {
-                  acn[k][ch] = lalpha[k] * lnrm[k][ch] + (1.f - lalpha[k]) * acn[k][ch];
-                  lnrm[k][ch] = nrm[ch];
-                  dL_dalpha += (nrm[ch] - acn[k][ch]) * dpn[k][ch];
-                  v[11 + ch] += dchannel_dcolor * dpn[k][ch] * 10;
-                }
+                for (int ch = 0; ch < 3; ++ch) v[11 + ch] += dcn * dpn[k][ch];
               }
-              {
-                const float d_cur = cd.x - (ddx[k] * ne.w + ddy[k] * zyj);
-                acd[k] = lalpha[k] * ldep[k] + (1.f - lalpha[k]) * acd[k];
-                ldep[k] = d_cur;
-                // RS backward.cu:842-850: dpd*D/(1-Tf)^2 * -Tf / (1-alpha) / T, the first four factors hoisted (cN)
-                float dL_dalpha_depth = normalize_depth ? cN[k] * inv1ma * rcp_nr(T[k]) : 0.f;
-                dL_dalpha_depth += (d_cur - acd[k]) * dLc[k];
-                v[6] += dchannel_dcolor * dLc[k];
-                dL_dalpha += dL_dalpha_depth;
-              }
+              v[6] += dchannel_dcolor * dLc[k];
+              accA[k] = fmaf(lalpha[k], lastB[k] - accA[k], accA[k]);
+              lastB[k] = B;
+              float dL_dalpha = B - accA[k];
+              // RS backward.cu:842-850: dpd*D/(1-Tf)^2 * -Tf / (1-alpha) / T, the first four factors hoisted (cN)
+              if (normalize_depth) dL_dalpha = fmaf(cN[k] * inv1ma, rcp_nr(T[k]), dL_dalpha);
               dL_dalpha *= T[k];
               dL_dalpha += dpoT[k] * inv1ma;
               lalpha[k] = alpha;
