@@ -286,28 +286,36 @@ __global__ void __launch_bounds__(kRThreads) r3_render_fwd_kernel(
           pw[1] = -0.5f * (co.x * dx1 * dx1 + co.z * dy0 * dy0) - co.y * dx1 * dy0;
           pw[2] = -0.5f * (co.x * dx0 * dx0 + co.z * dy1 * dy1) - co.y * dx0 * dy1;
           pw[3] = -0.5f * (co.x * dx1 * dx1 + co.z * dy1 * dy1) - co.y * dx1 * dy1;
-          // Branch-free blend step: a pixel that does not take this Gaussian adds a zero weight and keeps its
-          // T / last (selects), so the 2x2 quad runs as straight-line code.  Arithmetic of a taken step is
-          // unchanged ((c*alpha)*T + C, T*(1-alpha)), n_contrib / n_touched stay bit-identical to the reference.
-          const float4 cd = sm.c[cur][j];
-          const uint32_t pos = (uint32_t)(r * kRBatch + j + 1);
-          int touched = 0;
+          float al[4];
+          bool any = false;
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            const float alpha = fminf(0.99f, co.w * expf(pw[k]));
-            const bool c = !done[k] && !(pw[k] > 0.0f) && !(alpha < 1.0f / 255.0f);
-            const float test_T = T[k] * (1 - alpha);
-            const bool low = test_T < 0.0001f;
-            const bool upd = c && !low;
-            done[k] = done[k] || (c && low);
-            const float w = upd ? alpha : 0.f;
-            C0[k] += cd.y * w * T[k];
-            C1[k] += cd.z * w * T[k];
-            C2[k] += cd.w * w * T[k];
-            Dp[k] += cd.x * w * T[k];
-            touched += (upd && test_T > 0.5f) ? 1 : 0;
-            T[k] = upd ? test_T : T[k];
-            last[k] = upd ? pos : last[k];
+            al[k] = fminf(0.99f, co.w * expf(pw[k]));
+            const bool c = !done[k] && !(pw[k] > 0.0f) && !(al[k] < 1.0f / 255.0f);
+            if (!c) al[k] = -1.f;
+            any |= c;
+          }
+          int touched = 0;
+          if (any) {
+            const float4 cd = sm.c[cur][j];
+            const uint32_t pos = (uint32_t)(r * kRBatch + j + 1);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              if (al[k] >= 0.f) {
+                const float test_T = T[k] * (1 - al[k]);
+                if (test_T < 0.0001f) {
+                  done[k] = true;
+                } else {
+                  C0[k] += cd.y * al[k] * T[k];
+                  C1[k] += cd.z * al[k] * T[k];
+                  C2[k] += cd.w * al[k] * T[k];
+                  Dp[k] += cd.x * al[k] * T[k];
+                  if (test_T > 0.5f) ++touched;
+                  T[k] = test_T;
+                  last[k] = pos;
+                }
+              }
+            }
           }
           const int tsum = __reduce_add_sync(0xffffffffu, touched);
           if (tsum && lane == 0) atomicAdd(&n_touched[sm.id[cur][j]], tsum);
