@@ -39,7 +39,9 @@ def _relmax(a, b):
     return ((a - b).abs().max() / (b.abs().max() + 1e-30)).item()
 
 
-@pytest.mark.parametrize("P,W,H,seed", [(2000, 320, 200, 3), (50000, 640, 360, 1), (30000, 333, 217, 5)])
+# last case = BASELINE.json configs[1] at full size (the bench.py C2 scene: 500k Gaussians, 1226x370, ~22.7M instances)
+@pytest.mark.parametrize("P,W,H,seed", [(2000, 320, 200, 3), (50000, 640, 360, 1), (30000, 333, 217, 5),
+                                        (500000, 1226, 370, 0)])
 def test_forward_bitexact_and_backward(P, W, H, seed):
     from oracle.ref_api import RefRaster3, available
     from pings_b200 import _raster_c as RC
