@@ -40,6 +40,37 @@ def _relmax(a, b):
 
 
 # last case = BASELINE.json configs[1] at full size (the bench.py C2 scene: 500k Gaussians, 1226x370, ~22.7M instances)
+
+@pytest.mark.gpu
+def test_c5_large_map_forward_only():
+    """BASELINE.json configs[4] shape: one 1080p novel view of a 5M-Gaussian map, forward only (inspect_pings-style
+    rendering).  Small Gaussians (a large map seen from inside) keep the instance count near 10^8."""
+    from oracle.ref_api import RefRaster3, available
+    from pings_b200 import _raster_c as RC
+    if not available("ref_r3"):
+        pytest.fail("oracle/_ref/libref_r3.so missing: run __graft_entry__.build() where /root/reference exists")
+    P, W, H, seed = 5_000_000, 1920, 1080, 4
+    cam = synth.hd_camera(seed, W, H)
+    sc = {k: v.cuda() for k, v in synth.gaussians_in_view(cam, P, seed, scale_lo=0.004, scale_hi=0.05).items()}
+    mats = [m.cuda() for m in cam.matrices()]
+    view, full, proj, center = mats
+    bg = torch.zeros(3, device="cuda")
+    with torch.no_grad():
+        R, color, radii, geom, binning, img, depth, opac, n_touched = _mine_forward(cam, sc, mats, W, H, bg, debug=False)
+    ref = RefRaster3()
+    r = ref.forward(sc, (view, full, proj), W, H, cam.tanfovx, cam.tanfovy, bg, campos=center)
+    assert R == r["num_rendered"] and R > 10 * P // 2
+    assert torch.equal(radii, r["radii"])
+    dv = RC.debug_views(0, P, W, H, R, geom, binning, img)
+    assert torch.equal(dv["ranges"], r["ranges"])
+    assert torch.equal(dv["point_list"], r["point_list"])
+    assert torch.equal(dv["n_contrib"], r["n_contrib"])
+    assert torch.equal(n_touched, r["n_touched"])
+    torch.testing.assert_close(color, r["color"], rtol=IMG_RTOL, atol=IMG_ATOL)
+    torch.testing.assert_close(depth, r["depth"], rtol=IMG_RTOL, atol=IMG_ATOL)
+    torch.testing.assert_close(opac, r["opacity"], rtol=IMG_RTOL, atol=IMG_ATOL)
+
+
 @pytest.mark.parametrize("P,W,H,seed", [(2000, 320, 200, 3), (50000, 640, 360, 1), (30000, 333, 217, 5),
                                         (500000, 1226, 370, 0)])
 def test_forward_bitexact_and_backward(P, W, H, seed):
