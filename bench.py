@@ -24,6 +24,7 @@ arm falls back to the CPU restatement.
 from __future__ import annotations
 
 import argparse
+from types import SimpleNamespace
 import json
 import os
 import statistics
@@ -656,6 +657,126 @@ def surfel_leg(args, local) -> dict:
                                              "frac": round(ssim_gbs / pk["hbm_gbs"], 4), "alg_bytes_per_elem": 52}}}
 
 
+# ----------------------------------------------------------------------------------------------
+# Config C4 (BASELINE.json configs[3]): one PINGS mapping step with the KITTI-GS decoder shapes
+# (config/run_kitti_gs.yaml:21-30: feature_dim 32, color_feature_dim 16, gs_mlp_hidden_dim 128, 8 Gaussians per
+# neural point, view_concat_on, learn_color_residual): render() = spawn_gaussians (5 decoder heads) + surfel
+# rasterizer, photometric L1 + fused-SSIM + depth L1 loss, backward to the neural-point features and decoder
+# weights, plus the SDF branch (query_feature + geo decoder on bs / world rows).  The 8 views of a batch are sharded
+# one per rank (weak scaling: one view per GPU per step); the exchange step is ONE all-reduce of the flat
+# [geo features | colour features | decoder weights] gradient buffer.  Reported under extra.mapping_step.
+C4 = dict(N=60_000, Fg=32, Fc=16, hidden=128, level=1, K=8, W=1226, H=370, res=0.4, sdf_bs=16384, seed=5)
+
+
+class _ViewCam(SimpleNamespace):
+    def full_patch(self, down_rate=0):
+        s = 2 ** down_rate
+        return torch.tensor([0, 0, int(self.image_height / s) - 1, int(self.image_width / s) - 1], dtype=torch.float32,
+                            device=self.device)
+
+
+def mapping_leg(args, local, world, rank) -> dict:
+    import math
+    from pings_b200 import synth, synth_neural as SN
+    from pings_b200.decoder import Decoder
+    from pings_b200.fused_ssim import fused_ssim
+    from pings_b200.gaussian_renderer import render
+    from pings_b200.neural_points import default_config
+    from pings_b200.parallel import FlatGradAllReduce, shard_rows
+    dev = torch.device("cuda", local)
+    N, Fg, Fc, Hd, Lv, K, W, H = (C4[k] for k in ("N", "Fg", "Fc", "hidden", "level", "K", "W", "H"))
+    g = torch.Generator().manual_seed(C4["seed"])
+    cam0 = synth.kitti_camera(C4["seed"], W, H)
+    T = cam0.T_wc.clone()
+    T[:3, 3] += T[:3, 2] * (0.1 * rank)          # this rank's view of the batch
+    cam = synth.Camera(cam0.W, cam0.H, cam0.fx, cam0.fy, cam0.cx, cam0.cy, T)
+    view, full, proj, center = [m.to(dev) for m in cam.matrices()]
+    vc = _ViewCam(device=dev, uid=rank, image_width=W, image_height=H, FoVx=2 * math.atan(cam.tanfovx),
+                  FoVy=2 * math.atan(cam.tanfovy), zfar=100.0, fx=cam.fx, fy=cam.fy,
+                  prcppoint=torch.tensor([cam.cx / W, cam.cy / H], device=dev), projection_matrix=proj,
+                  world_view_transform=view, full_proj_transform=full, camera_center=center,
+                  cam_rot_delta=torch.zeros(3, device=dev, requires_grad=True),
+                  cam_trans_delta=torch.zeros(3, device=dev, requires_grad=True),
+                  exposure_mat=torch.eye(3, device=dev).requires_grad_(True),
+                  exposure_offset=torch.zeros(1, 3, device=dev).requires_grad_(True),
+                  exposure_a=torch.zeros(1, device=dev), exposure_b=torch.zeros(1, device=dev))
+    # neural points on "surfaces" in front of camera 0: log-uniform depth 3..60 m inside the frustum (same on every rank)
+    z = torch.exp(torch.rand(N, generator=g) * (math.log(60.0) - math.log(3.0)) + math.log(3.0))
+    x = (torch.rand(N, generator=g) - 0.5) * 2.1 * cam0.tanfovx * z
+    y = (torch.rand(N, generator=g) - 0.5) * 2.1 * cam0.tanfovy * z
+    pc = torch.stack([x, y, z, torch.ones(N)], 1).double()
+    pos = (cam0.T_wc @ pc.T).T[:, :3].float().to(dev)
+    quat = torch.zeros(N, 4)
+    quat[:, 0] = 1.0
+    data = {"position": pos, "orientation": quat.to(dev), "color": torch.rand(N, 3, generator=g).to(dev),
+            "geo_feature": (0.1 * torch.randn(N + 1, Fg, generator=g)).to(dev).requires_grad_(True),
+            "color_feature": (0.1 * torch.randn(N + 1, Fc, generator=g)).to(dev).requires_grad_(True),
+            "resolution": C4["res"]}
+    cfg = default_config(device=dev)
+    torch.manual_seed(C4["seed"])                  # identical decoder weights on every rank
+    decs = {"gauss_xyz": Decoder(cfg, Fg, Hd, Lv, 3, K, 0), "gauss_rot": Decoder(cfg, Fg, Hd, Lv, 4, K, 0),
+            "gauss_scale": Decoder(cfg, Fg, Hd, Lv, 3, K, 0), "gauss_alpha": Decoder(cfg, Fg, Hd, Lv, 1, K, 0),
+            "gauss_color": Decoder(cfg, Fc, Hd, Lv, 3, K, 3)}
+    for d in decs.values():
+        d.to(dev)
+    # SDF branch: the PIN-SLAM shaped map / geo decoder of the C1 leg, bs rows split over the ranks
+    npm, sdf_dec, q = SN.c1_map_and_queries(device=dev)
+    lo, hi = shard_rows(C4["sdf_bs"], rank, world)
+    qb = q[lo:hi].clone()
+    sdf_target = torch.zeros(hi - lo, device=dev)
+    gt = torch.Generator().manual_seed(91 + rank)
+    target = torch.rand(3, H, W, generator=gt).to(dev)
+    target_d = (torch.rand(1, H, W, generator=gt) * 40 + 3).to(dev)
+    bg = torch.zeros(3, device=dev)
+    params = [data["geo_feature"], data["color_feature"], npm.local_geo_features]
+    for d in list(decs.values()) + [sdf_dec]:
+        params += [p for p in d.parameters()]
+    exchange = FlatGradAllReduce(params, average=True)
+    info = {}
+
+    def step():
+        for p in params + [vc.cam_rot_delta, vc.cam_trans_delta, vc.exposure_mat, vc.exposure_offset]:
+            p.grad = None
+        res = render(vc, None, data, decs, None, bg, view_concat_on=True, learn_color_residual=True,
+                     gs_type="gaussian_surfel", d2n_on=False)
+        rgb = res["render"]
+        loss = 0.8 * (rgb - target).abs().mean() + 0.2 * (1.0 - fused_ssim(rgb.unsqueeze(0), target.unsqueeze(0)))
+        loss = loss + 0.05 * (res["surf_depth"] - target_d).abs().mean() + 0.01 * res["rend_alpha"].mean()
+        geo, _, w, cnt, _ = npm.query_feature(qb, accumulate_stability=False)
+        loss = loss + 0.5 * (sdf_dec.sdf(geo) - sdf_target).abs().mean()
+        loss.backward()
+        exchange()
+        info["gaussians"] = int(res["gaussian_xyz"].shape[0])
+        return loss
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    steps, warm = max(3, min(args.steps, 10)), 3
+    for _ in range(warm):
+        step()
+    barrier(world)
+    evs = []
+    for _ in range(steps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        step()
+        b.record()
+        evs.append((a, b))
+    barrier(world)
+    t = torch.tensor([sum(a.elapsed_time(b) for a, b in evs) / steps], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    return {"mapping_step": {"metric": "PINGS mapping steps (views)/s: render() + loss + backward + SDF branch + exchange (C4)",
+                             "value": round(world / (ms * 1e-3), 2), "unit": "views/s", "ms_per_step": round(ms, 4),
+                             "mpix_per_s": round(world * W * H / (ms * 1e-3) / 1e6, 2),
+                             "neural_points": N, "gaussians_per_point": K, "gaussians_rendered": info.get("gaussians"),
+                             "decoder": f"{Fg}+0/{Fc}+3 -> {Hd} x{Lv} -> K*out (5 heads)", "sdf_rows_per_rank": hi - lo,
+                             "exchange_bytes": exchange.nbytes if world > 1 else 0,
+                             "note": "one view per GPU per step (a batch of `world` views), eager spawn_gaussians glue "
+                                     "included; host-driven, timed with CUDA events, L2 flushed between steps"}}
+
+
 def sdf_cpu_leg(budget_s: float = 15.0) -> dict:
     """The reference's PyTorch CPU SDF path restated (oracle/neural_cpu.py) on this box's host cores."""
     from oracle import neural_cpu as O
@@ -753,8 +874,13 @@ def main():
         sdf = sdf_leg(args, local, world, rank)
     except Exception as ex:
         sdf = {"sdf": f"failed: {ex!r}"}
+    try:  # C4: every rank renders its view of the batch and joins the gradient exchange
+        mapping = mapping_leg(args, local, world, rank)
+    except Exception as ex:
+        mapping = {"mapping_step": f"failed: {ex!r}"}
     if rank == 0:
         line.setdefault("extra", {}).update(sdf)
+        line["extra"].update(mapping)
         if world == 1:
             try:
                 line["extra"].update(surfel_leg(args, local))

@@ -13,6 +13,7 @@ print("value", d["value"], "ms", d["ms_per_step"], "e2e", d["e2e"]["value"], "se
 print(" ".join(f"{k}={v['ms']}" for k, v in d["roofline"]["phases"].items()))
 x = d["extra"]
 print("c3 phases", x["surfel_ssim"].get("phases_ms"))
+print("mapping", x.get("mapping_step"))
 print("sdf", x["sdf"]["value"], x["sdf"]["ms_per_step"], "train", x["sdf"]["train_fwd_bwd_bs10000"]["ms_per_step"],
       "surfel", x["surfel_ssim"]["value"], x["surfel_ssim"]["ms_per_step"], "mlp", x["mlp_batch"]["ms_per_step"])
 PY
