@@ -405,7 +405,7 @@ def run_ours(args, rank, world, local):
 
 
 # per-launch dram bytes of the dominant kernels from profiles/ (ncu --set full), filled in as captured
-# (profiles/r01_ncu_full_c2_v6.csv: dram__bytes_read.sum + dram__bytes_write.sum, summed over the
+# (profiles/r01_ncu_full_c2_v7.csv: dram__bytes_read.sum + dram__bytes_write.sum, summed over the
 # kernels of a phase; the capture runs the step without the L2 flush, so inputs produced by the previous
 # kernel are L2 hits)
 TRAFFIC: dict = {"preprocess_fwd": 29.0e6, "depth_sort": 6.05e6, "binning": 82.5e6, "render_fwd": 3.41e6,
