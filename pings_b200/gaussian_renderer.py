@@ -100,19 +100,23 @@ def spawn_gaussians(neural_points_data: Dict, decoders: Dict, visible_mask: Opti
     elif valid_mask is not None:
         spawn_mask = valid_mask
     if spawn_mask is not None:
-        position = position[spawn_mask]
-        orientation = orientation[spawn_mask]
+        # One nonzero (one host sync) and index_select gathers instead of a boolean-mask index per tensor
+        # (GR:556-569 indexes each tensor with the mask: same rows, same order; every mask index costs a
+        # nonzero + a sync forward and a sort-based index_put backward).
+        sidx = torch.nonzero(spawn_mask).view(-1)
+        position = position.index_select(0, sidx)
+        orientation = orientation.index_select(0, sidx)
         if color is not None:
-            color = color[spawn_mask]
+            color = color.index_select(0, sidx)
         if free_mask is not None:
-            free_mask = free_mask[spawn_mask]
+            free_mask = free_mask.index_select(0, sidx)
         if stability is not None:
-            stability = stability[spawn_mask]
-        # index list padded with -1 (the feature tables carry a trailing padding row), GR:563-569 / quirk q19
-        visible_idx = torch.nonzero(spawn_mask)
-        visible_idx = torch.cat((visible_idx.view(-1), torch.tensor([-1]).to(visible_idx)))
-        geo_features = geo_features[visible_idx]
-        color_features = color_features[visible_idx]
+            stability = stability.index_select(0, sidx)
+        # index list padded with -1 = the trailing padding row of the feature tables, GR:563-569 / quirk q19
+        visible_idx = torch.cat((sidx, sidx.new_full((1,), geo_features.shape[0] - 1)))
+        geo_features = geo_features.index_select(0, visible_idx)
+        color_features = color_features.index_select(
+            0, torch.cat((sidx, sidx.new_full((1,), color_features.shape[0] - 1))))
     if position.shape[0] < 10:
         return None
 
@@ -183,10 +187,12 @@ def spawn_gaussians(neural_points_data: Dict, decoders: Dict, visible_mask: Opti
 
     def _keep(mask):
         nonlocal gaussian_xyz, gaussian_scale, gaussian_rot, gaussian_alpha, gaussian_color, gaussian_free_mask
-        gaussian_xyz, gaussian_scale, gaussian_rot = gaussian_xyz[mask], gaussian_scale[mask], gaussian_rot[mask]
-        gaussian_alpha, gaussian_color = gaussian_alpha[mask], gaussian_color[mask]
+        kidx = torch.nonzero(mask).view(-1)   # one compaction index for all six tensors (see above)
+        gaussian_xyz, gaussian_scale = gaussian_xyz.index_select(0, kidx), gaussian_scale.index_select(0, kidx)
+        gaussian_rot, gaussian_alpha = gaussian_rot.index_select(0, kidx), gaussian_alpha.index_select(0, kidx)
+        gaussian_color = gaussian_color.index_select(0, kidx)
         if gaussian_free_mask is not None:
-            gaussian_free_mask = gaussian_free_mask[mask]
+            gaussian_free_mask = gaussian_free_mask.index_select(0, kidx)
 
     if alpha_filter_on:
         _keep(gaussian_alpha.squeeze(-1) > 0.0)
@@ -199,6 +205,9 @@ def spawn_gaussians(neural_points_data: Dict, decoders: Dict, visible_mask: Opti
         "gaussian_free_mask": gaussian_free_mask, "local_view_gaussian_count": gaussian_xyz.shape[0],
         "shifted_position": shifted_position,
     }
+
+
+_SURFEL_CFG: Dict = {}
 
 
 # ---- render (GR:27-466) --------------------------------------------------------------------------
@@ -247,7 +256,10 @@ def render(viewpoint_camera, cam_pose: Optional[torch.Tensor], neural_points_dat
                   projmatrix=viewpoint_camera.full_proj_transform, projmatrix_raw=viewpoint_camera.projection_matrix,
                   sh_degree=0, campos=viewpoint_camera.camera_center, prefiltered=False, debug=False)
     if gs_type == "gaussian_surfel":
-        cfg = torch.tensor([True, True, True, True, front_only_on], dtype=dtype, device=device)  # GR:137-142
+        key = (str(device), bool(front_only_on))   # GR:137-142; cached: torch.tensor(list, device=cuda) is a blocking H2D copy
+        cfg = _SURFEL_CFG.get(key)
+        if cfg is None:
+            cfg = _SURFEL_CFG[key] = torch.tensor([True, True, True, True, front_only_on], dtype=dtype, device=device)
         raster_settings = GaussianRasterizationSettings(patch_bbox=viewpoint_camera.full_patch(down_rate),
                                                         prcppoint=viewpoint_camera.prcppoint, config=cfg, **common)
     else:
