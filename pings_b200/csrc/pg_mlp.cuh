@@ -119,10 +119,9 @@ __global__ void __launch_bounds__(kMlpThreads) mlp_forward_kernel(MlpDev m, long
 __device__ __forceinline__ void mlp_dgrad_tile(const float* __restrict__ g, float* __restrict__ out, int ld,
                                                const float* __restrict__ Wg, float* __restrict__ Ws, int Din, int Dout) {
   const int Dp = (Din + 3) / 4 * 4;
-  for (int i = threadIdx.x; i < Dout * Dp; i += kMlpThreads) {
-    const int u = i / Dp, f = i - u * Dp;
-    Ws[i] = f < Din ? Wg[(size_t)u * Din + f] : 0.f;
-  }
+  // warp per row, lanes along the row: no per-element integer division (it was about half of this kernel's instructions)
+  for (int u = threadIdx.x >> 5; u < Dout; u += kMlpThreads / 32)
+    for (int f = threadIdx.x & 31; f < Dp; f += 32) Ws[u * Dp + f] = f < Din ? Wg[(size_t)u * Din + f] : 0.f;
   __syncthreads();
   const int rg = threadIdx.x >> 4, fl = threadIdx.x & 15;
   for (int f0 = fl * 4; f0 < Dp; f0 += 64) {
@@ -176,17 +175,14 @@ __global__ void __launch_bounds__(kMlpThreads) mlp_backward_kernel(MlpDev m, Mlp
   float* DIN = IN + kMlpRows * ld;        // gradient w.r.t. that input
   float* Ws = DIN + kMlpRows * ld;
   const long long r0 = (long long)blockIdx.x * kMlpRows;
-  for (int i = threadIdx.x; i < kMlpRows * m.out_dim; i += kMlpThreads) {
-    const int r = i / m.out_dim, u = i - r * m.out_dim;
-    G[r * ld + u] = (r0 + r < N) ? dY[(r0 + r) * m.out_dim + u] : 0.f;
-  }
+  const int wrp = threadIdx.x >> 5, lan = threadIdx.x & 31;
+  for (int r = wrp; r < kMlpRows; r += kMlpThreads / 32)
+    for (int u = lan; u < m.out_dim; u += 32) G[r * ld + u] = (r0 + r < N) ? dY[(r0 + r) * m.out_dim + u] : 0.f;
   for (int l = m.levels; l >= 0; --l) {
     const int Din = mlp_layer_in(m, l), Dout = mlp_layer_out(m, l);
     const float* src = l == 0 ? x : hsave + (size_t)(l - 1) * N * m.hidden;
-    for (int i = threadIdx.x; i < kMlpRows * Din; i += kMlpThreads) {
-      const int r = i / Din, f = i - r * Din;
-      IN[r * ld + f] = (r0 + r < N) ? src[(r0 + r) * Din + f] : 0.f;
-    }
+    for (int r = wrp; r < kMlpRows; r += kMlpThreads / 32)
+      for (int f = lan; f < Din; f += 32) IN[r * ld + f] = (r0 + r < N) ? src[(r0 + r) * Din + f] : 0.f;
     __syncthreads();
     // weight / bias gradients of this tile -> global accumulation.  Register tile: thread (ul, fl) of a 16 x 16
     // arrangement owns outputs u = ul + 16 a, inputs f = fl + 16 b, four of each at a time: 8 shared loads per
@@ -240,17 +236,16 @@ __global__ void __launch_bounds__(kMlpThreads) mlp_backward_kernel(MlpDev m, Mlp
     mlp_dgrad_tile(G, DIN, ld, m.W[l], Ws, Din, Dout);
     if (l > 0) {
       // through the activation of layer l-1 (its post-activation output is IN)
-      for (int i = threadIdx.x; i < kMlpRows * Din; i += kMlpThreads) {
-        const int r = i / Din, f = i - r * Din;
-        const float h = IN[r * ld + f];
-        G[r * ld + f] = DIN[r * ld + f] * (h > 0.f ? 1.f : (m.leaky ? 0.01f : 0.f));
-      }
+      for (int r = wrp; r < kMlpRows; r += kMlpThreads / 32)
+        for (int f = lan; f < Din; f += 32) {
+          const float h = IN[r * ld + f];
+          G[r * ld + f] = DIN[r * ld + f] * (h > 0.f ? 1.f : (m.leaky ? 0.01f : 0.f));
+        }
       __syncthreads();
     } else {
-      for (int i = threadIdx.x; i < kMlpRows * Din; i += kMlpThreads) {
-        const int r = i / Din, f = i - r * Din;
-        if (r0 + r < N) dX[(r0 + r) * Din + f] = DIN[r * ld + f];
-      }
+      for (int r = wrp; r < kMlpRows; r += kMlpThreads / 32)
+        for (int f = lan; f < Din; f += 32)
+          if (r0 + r < N) dX[(r0 + r) * Din + f] = DIN[r * ld + f];
     }
   }
 }
