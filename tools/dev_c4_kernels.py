@@ -30,3 +30,7 @@ for e in ev:
     a = agg.setdefault(e.name[:80], [0, 0.0]); a[0] += 1; a[1] += e.device_time
 for k, v in sorted(agg.items(), key=lambda x: -x[1][1])[:28]:
     print(f"{v[1]/3:9.1f} us  x{v[0]//3:<3d} {k}")
+
+print("by count:")
+for k, v in sorted(agg.items(), key=lambda x: -x[1][0])[:22]:
+    print(f"x{v[0]//3:<4d} {v[1]/3:9.1f} us  {k}")
