@@ -735,7 +735,8 @@ def mapping_leg(args, local, world, rank) -> dict:
     info = {}
 
     def step():
-        for p in params + [vc.cam_rot_delta, vc.cam_trans_delta, vc.exposure_mat, vc.exposure_offset]:
+        exchange.attach()   # grads are views of the flat exchange buffer, zeroed: no pack / scatter copies
+        for p in (vc.cam_rot_delta, vc.cam_trans_delta, vc.exposure_mat, vc.exposure_offset):
             p.grad = None
         res = render(vc, None, data, decs, None, bg, view_concat_on=True, learn_color_residual=True,
                      gs_type="gaussian_surfel", d2n_on=False)

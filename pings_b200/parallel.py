@@ -58,12 +58,27 @@ class FlatGradAllReduce:
         self.stream = torch.cuda.Stream(device=dev) if (side_stream and dev.type == "cuda") else None
         self._work = None
 
+    def attach(self) -> None:
+        """Make every `p.grad` a view of the flat buffer and zero it: autograd then accumulates straight into
+        the buffer (AccumulateGrad adds in place into an existing .grad), so `launch()` / `wait()` need no
+        pack / scatter copies (2 copies per parameter per step otherwise).  Call once per step INSTEAD of
+        setting the grads to None; a caller that replaces `p.grad` afterwards simply falls back to the copies."""
+        self.flat.zero_()
+        for p, v in zip(self.params, self.views):
+            p.grad = v.view(p.shape)
+
+    def _attached(self, p: torch.Tensor, v: torch.Tensor) -> bool:
+        g = p.grad
+        return g is not None and g.data_ptr() == v.data_ptr() and g.numel() == v.numel() and g.is_contiguous()
+
     @property
     def nbytes(self) -> int:
         return self.flat.numel() * self.flat.element_size()
 
     def pack(self) -> None:
         for p, v in zip(self.params, self.views):
+            if self._attached(p, v):
+                continue
             if p.grad is None:
                 v.zero_()
             else:
@@ -91,6 +106,8 @@ class FlatGradAllReduce:
         if self.stream is not None:
             torch.cuda.current_stream(self.flat.device).wait_stream(self.stream)
         for p, v in zip(self.params, self.views):
+            if self._attached(p, v):
+                continue
             if p.grad is None:
                 p.grad = v.reshape(p.shape).clone()
             else:

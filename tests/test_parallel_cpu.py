@@ -71,6 +71,26 @@ def _worker(rank: int, ws: int, port: int, q):
             if rank == 1:
                 a[0, 0] += 1e-3
         ok &= not PP.replicas_in_sync([a, b, c])
+        # attached mode: grads are views of the flat buffer, autograd accumulates into it, no pack / scatter copies
+        torch.manual_seed(1)
+        a2 = torch.nn.Parameter(torch.randn(5, 3))
+        b2 = torch.nn.Parameter(torch.randn(7))
+        c2 = torch.nn.Parameter(torch.randn(2, 2))
+        red2 = PP.FlatGradAllReduce([a2, b2, c2], average=True)
+        for _ in range(2):   # second step: attach() must clear the previous step's sums
+            red2.attach()
+            l2 = (x @ a2).sum() + (b2 * (rank + 1)).sum() + (x @ a2).pow(2).sum()
+            if rank == 0:
+                l2 = l2 + (c2 ** 2).sum()
+            l2.backward()
+            ok &= a2.grad.data_ptr() == red2.views[0].data_ptr()
+            loc2 = [p.grad.clone() for p in (a2, b2, c2)]
+            red2()
+            for p, t in zip((a2, b2, c2), loc2):
+                gl = [torch.zeros_like(t) for _ in range(ws)]
+                dist.all_gather(gl, t)
+                ok &= torch.allclose(p.grad, torch.stack(gl).mean(0), rtol=0, atol=1e-6)
+                ok &= p.grad.data_ptr() >= red2.flat.data_ptr()
         # query-row sharding: the union of the shards reproduces the full result
         full = torch.arange(10, dtype=torch.float32) ** 2
         lo, hi = PP.shard_rows(10, rank, ws)
