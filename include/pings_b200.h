@@ -151,6 +151,14 @@ int pg_raster_debug_views(int variant, int P, int width, int height, int64_t num
                           const float** final_T, const uint32_t** n_contrib,
                           const float** records /* float4[3P] */, const uint32_t** depth_sorted_idx);
 
+/* Debug/parity accessor: the per-Gaussian gradient accumulation records the blend backward fills (valid after
+ * pg_raster_backward).  *gacc points at P * stride float4: 3DGS stride 3 = (dmean2D.xy, dconic.x, dconic.y)
+ * (dconic.w, dopacity, ddepth, 0) (dcolor.rgb, 0); surfel stride 4 adds (dnormal.xyz (x10), 0) and keeps the
+ * sum of dL_dpixD in the 4th lane of record 1 (the per-pixel-depth term of RS backward.cu:894-897 is applied
+ * in the per-surfel kernel).  These are the reference's dL_dconic / dL_ddepths / dL_dnormal scratch tensors
+ * (RS rasterize_points.cu:176-188), which it never returns either. */
+int pg_raster_debug_gacc(int variant, int P, void* geom_ws, const float** gacc, int* stride_float4);
+
 /* Measurement accessor: number of (Gaussian, tile row, 32-tile band) records the band binning of the
  * last stage 2 on this workspace produced (synchronises `stream`); -1 when the tile grid used another
  * binning path.  Used by bench.py for the algorithmic byte count; no reference counterpart. */

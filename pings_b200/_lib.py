@@ -120,6 +120,8 @@ def lib() -> C.CDLL:
                                      C.POINTER(PgRasterBwdIn), C.POINTER(PgRasterBwdOut), fp]
     L.pg_raster_debug_views.restype = C.c_int
     L.pg_raster_debug_views.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int64, fp, fp, fp] + [C.POINTER(fp)] * 6
+    L.pg_raster_debug_gacc.restype = C.c_int
+    L.pg_raster_debug_gacc.argtypes = [C.c_int, C.c_int, fp, C.POINTER(fp), C.POINTER(C.c_int)]
     L.pg_raster_band_records.restype = C.c_int64
     L.pg_raster_band_records.argtypes = [C.c_int, C.c_int, C.c_int64, fp, fp]
     L.pg_photo_depth_loss_forward.restype = C.c_int

@@ -330,3 +330,20 @@ def debug_views(variant, P, W, H, R, geom, binning, img):
         records=view(geom, outs[4], 12 * P, torch.float32).view(P, 3, 4),
         depth_sorted_idx=view(geom, outs[5], P, torch.int32),
     )
+
+
+def debug_blend_sums(variant, P, geom):
+    """The blend backward's per-Gaussian sums (valid after the backward ran on `geom`), as typed views:
+    means2D [P,2] (without the surfel per-pixel-depth term), conic [P,3] = (x, y, w), opacity [P], depths [P],
+    colors [P,3], and for surfels normal [P,3] (x10) and dpixD_sum [P]."""
+    lib = L.lib()
+    p, stride = C.c_void_p(), C.c_int(0)
+    L.check(lib.pg_raster_debug_gacc(variant, P, geom.data_ptr(), C.byref(p), C.byref(stride)), "debug gacc")
+    off = p.value - geom.data_ptr()
+    rec = geom[off:off + 16 * stride.value * P].view(torch.float32).view(P, stride.value, 4)
+    out = dict(means2D=rec[:, 0, :2], conic=torch.stack([rec[:, 0, 2], rec[:, 0, 3], rec[:, 1, 0]], 1),
+               opacity=rec[:, 1, 1], depths=rec[:, 1, 2], colors=rec[:, 2, :3])
+    if stride.value == 4:
+        out["normal"] = rec[:, 3, :3]
+        out["dpixD_sum"] = rec[:, 1, 3]
+    return out

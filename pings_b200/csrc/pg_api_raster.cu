@@ -260,6 +260,15 @@ int pg_raster_debug_views(int variant, int P, int width, int height, int64_t num
   return PG_OK;
 }
 
+int pg_raster_debug_gacc(int variant, int P, void* geom_ws, const float** gacc, int* stride_float4) {
+  if (!geom_ws || !gacc || P < 0) return PG_ERR_ARG;
+  GeomWs gw;
+  carve_geom(variant, P, geom_ws, &gw);
+  *gacc = reinterpret_cast<const float*>(gw.gacc);
+  if (stride_float4) *stride_float4 = variant == PG_VARIANT_SURFEL ? 4 : 3;
+  return PG_OK;
+}
+
 int64_t pg_raster_band_records(int width, int height, int64_t num_rendered, void* binning_ws, void* stream) {
   const int gx = div_up(width, kTile), gy = div_up(height, kTile);
   if (!binning_ws || num_rendered <= 0 || !band_path(gx, gy)) return -1;

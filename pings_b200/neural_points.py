@@ -34,7 +34,8 @@ def default_config(**kw) -> SimpleNamespace:
                         query_nn_k=6, buffer_size=int(1e8), feature_dim=8, color_feature_dim=8, feature_std=0.0,
                         color_on=False, weighted_first=True, layer_norm_on=False, local_map_radius=84.0,
                         sorrounding_map_radius=84.0 * 1.4, local_map_travel_dist_ratio=5.0, diff_ts_local=400.0,
-                        track_on=True, temporal_local_map_off=False, use_mid_ts=False, range_filter_2d=False,
+                        track_on=True, temporal_local_map_off=False, use_mid_ts=False,
+                        range_filter_2d=True,   # utils/config.py:60
                         infer_bs=80000, mlp_bias_on=True, mlp_leaky_relu=False, main_loss_type="bce",
                         logistic_gaussian_ratio=0.55, sigma_sigmoid_m=0.1)
     for k, v in kw.items():
@@ -439,7 +440,9 @@ class NeuralPoints(nn.Module):
         self.local_free_gs_mask = self.free_gs_mask[local_mask]
         local_mask = torch.cat((local_mask, pad))
         self.local_mask = local_mask
-        g2l = torch.full((n + 1,), -1, dtype=torch.int64, device=dev)
+        # NP:455-457: `torch.full_like(local_mask, -1).long()` on a BOOL mask yields 1, not -1: points outside the
+        # local window map to local index 1 in the reference.  Kept (parity quirk; the kernels read the table as is).
+        g2l = torch.full((n + 1,), 1, dtype=torch.int64, device=dev)
         li = torch.nonzero(local_mask).flatten()
         g2l[li] = torch.arange(li.numel(), device=dev)
         g2l[-1] = -1
@@ -450,6 +453,42 @@ class NeuralPoints(nn.Module):
         self.local_orientation = sensor_orientation
         self.local_position = sensor_position.float()
 
+    def recreate_hash(self, sensor_position, sensor_orientation=None, kept_points: bool = True, with_ts: bool = True,
+                      cur_ts=0):
+        """NP:939-1024: rebuild the slot table from the stored points, one point per voxel (the one created
+        closest to cur_ts, or the most certain one); kept_points=False also drops the other points."""
+        res, dev = self.resolution, self.device
+        self.buffer_pt_index = torch.full((self.buffer_size,), -1, dtype=torch.int64, device=dev)
+        if with_ts:
+            used = ((self.point_ts_create + self.point_ts_update) / 2).int() if self.config.use_mid_ts else self.point_ts_create
+            value = torch.abs(used - cur_ts).float()
+        else:
+            value = self.point_certainties.max() - self.point_certainties
+        sample_idx = voxel_down_sample_min_value(self.neural_points, res, value)
+        if kept_points:
+            sp = self.neural_points[sample_idx]
+            self.buffer_pt_index[self._hash((sp / res).floor().to(torch.int64))] = sample_idx
+        else:
+            self.neural_points = self.neural_points[sample_idx]
+            self.point_orientations = self.point_orientations[sample_idx]
+            self.point_ts_create = self.point_ts_create[sample_idx]
+            self.point_ts_update = self.point_ts_update[sample_idx]
+            self.point_certainties = self.point_certainties[sample_idx]
+            if self.point_colors is not None:
+                self.point_colors = self.point_colors[sample_idx]
+            pad = torch.cat((sample_idx, sample_idx.new_full((1,), -1)))   # -1 = the trailing padding row
+            self.geo_features = self.geo_features[pad]
+            if self.color_features is not None:
+                self.color_features = self.color_features[pad]
+            self.valid_color_mask = self.valid_color_mask[sample_idx]
+            self.valid_gs_mask = self.valid_gs_mask[sample_idx]
+            self.free_gs_mask = self.free_gs_mask[sample_idx]
+            n = self.neural_points.shape[0]
+            self.buffer_pt_index[self._hash((self.neural_points / res).floor().to(torch.int64))] = torch.arange(
+                n, dtype=torch.int64, device=dev)
+        if sensor_position is not None:
+            self.reset_local_map(sensor_position, sensor_orientation, cur_ts)
+
     def assign_local_to_global(self):
         """NP:482-494."""
         lm = self.local_mask
@@ -458,6 +497,21 @@ class NeuralPoints(nn.Module):
         self.geo_features[lm] = self.local_geo_features.data
         if self.color_features is not None:
             self.color_features[lm] = self.local_color_features.data
+
+
+def voxel_down_sample_min_value(points: torch.Tensor, voxel_size: float, value: torch.Tensor) -> torch.Tensor:
+    """Index of the point with the smallest `value` in each occupied voxel (utils/tools.py:970-1010: value
+    quantised to 1000 levels relative to its maximum, ties -> lowest index)."""
+    g = torch.floor(points / voxel_size).long() - torch.floor(points.min(dim=0)[0] / voxel_size).long()
+    vs = g.max()
+    key = g[:, 0] + g[:, 1] * vs + g[:, 2] * vs * vs
+    uniq, inv = torch.unique(key, return_inverse=True)
+    ar = torch.arange(inv.numel(), dtype=torch.int64, device=points.device)
+    off = 10 ** len(str(inv.numel() - 1))
+    vq = (value / value.max() * 999).long()
+    best = torch.empty(uniq.shape, dtype=torch.int64, device=points.device).scatter_reduce_(
+        0, inv, ar + vq * off, reduce="amin", include_self=False)
+    return best % off
 
 
 def voxel_down_sample(points: torch.Tensor, voxel_size: float) -> torch.Tensor:
