@@ -151,3 +151,31 @@ def test_sdf_query_mirror_paths_agree():
         g1 = sq.get_numerical_gradient(q[:512], sdf_x=s_fused[:512], eps=0.02, two_side=False)
         assert torch.equal(g1[:, 0], (sq.sdf(q[:512] + e)[0] - s_fused[:512]) / 0.02)
         assert g2.shape == (512, 3) and g1.shape == (512, 3)
+
+
+def test_query_certainty_matches_reference_golden():
+    """NeuralPoints.query_certainty (NP:1117-1133) with the single-cell neighbourhood the mapper switches to
+    (utils/mapper.py:462-476) and with the default one, on the map the mirror's own update() builds on the GPU
+    from the three scans of tests/golden/maintenance.npz; the expected values come from the reference
+    (tests/golden/make_maintenance_golden.py).  A max over stored certainties: exact."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("t_maint", os.path.join(os.path.dirname(__file__), "test_maintenance_cpu.py"))
+    tm = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(tm)
+    G = tm.G
+    npm = tm.build_map("cuda")
+    tm.insert_scans(npm)
+    tm.apply_edits(npm)
+    assert np.array_equal(npm.neural_points.cpu().numpy(), G["assigned.neural_points"])   # GPU-built map == reference map
+    occ = torch.nonzero(npm.buffer_pt_index >= 0).flatten()
+    assert np.array_equal(occ.cpu().numpy(), G["assigned.hash_slots"])
+    assert np.array_equal(npm.buffer_pt_index[occ].cpu().numpy(), G["assigned.hash_values"])
+    q = torch.from_numpy(G["certainty.q"]).cuda()
+    npm.set_search_neighborhood(num_nei_cells=1, search_alpha=0.0)
+    assert npm.neighbor_K == int(G["certainty.K"][0]) == 7
+    c1 = npm.query_certainty(q)
+    npm.set_search_neighborhood(num_nei_cells=npm.config.num_nei_cells, search_alpha=npm.config.search_alpha)
+    c2 = npm.query_certainty(q)
+    assert np.array_equal(c1.cpu().numpy(), G["certainty.value"])
+    assert np.array_equal(c2.cpu().numpy(), G["certainty.value_default_nbh"])
+    assert float(c1[:20].abs().max()) == 0.0 and float(c1.max()) > 0.0

@@ -130,8 +130,10 @@ def test_forward_bitexact_and_backward(P, W, H, seed):
         assert _relmax(a, b) < 1e-4   # float atomics: run-to-run noise only (observed up to 2e-5)
 
 
-def test_sh_and_cov3d_precomp_paths():
-    """shs instead of colors_precomp (degree 2) and cov3D_precomp instead of scale/rotation."""
+@pytest.mark.parametrize("degree", [2, 3, 1])
+def test_sh_and_cov3d_precomp_paths(degree):
+    """shs instead of colors_precomp (degrees 1-3: R3 forward.cu:22-73, backward.cu:21-145; degree 3 uses all 16
+    coefficients, degree 1 reads 4 of 16) and cov3D_precomp instead of scale/rotation."""
     from oracle.ref_api import RefRaster3
     from pings_b200 import _raster_c as RC
     P, W, H, seed = 8000, 256, 192, 7
@@ -139,23 +141,26 @@ def test_sh_and_cov3d_precomp_paths():
     view, full, proj, center = mats
     bg = torch.zeros(3, device="cuda")
     g = torch.Generator().manual_seed(11)
-    sh = (torch.randn(P, 9, 3, generator=g) * 0.3).cuda()
-    R, color, radii, geom, binning, img, depth, opac, n_touched = _mine_forward(cam, sc, mats, W, H, bg, sh=sh, degree=2)
+    M = 9 if degree == 2 else 16
+    sh = (torch.randn(P, M, 3, generator=g) * 0.3).cuda()
+    R, color, radii, geom, binning, img, depth, opac, n_touched = _mine_forward(cam, sc, mats, W, H, bg, sh=sh, degree=degree)
     ref = RefRaster3()
-    r = ref.forward(sc, (view, full, proj), W, H, cam.tanfovx, cam.tanfovy, bg, sh=sh, degree=2, campos=center)
+    r = ref.forward(sc, (view, full, proj), W, H, cam.tanfovx, cam.tanfovy, bg, sh=sh, degree=degree, campos=center)
     assert R == r["num_rendered"]
     assert torch.equal(radii, r["radii"])
     torch.testing.assert_close(color, r["color"], rtol=IMG_RTOL, atol=IMG_ATOL)
     e = torch.empty(0)
     out = RC.rasterize_gaussians_backward(bg, sc["means3D"], radii, e, sc["scales"], sc["rotations"], 1.0, e, view, full,
-                                          proj, cam.tanfovx, cam.tanfovy, ct["color"], ct["depth"], sh, 2, center, geom,
+                                          proj, cam.tanfovx, cam.tanfovy, ct["color"], ct["depth"], sh, degree, center, geom,
                                           R, binning, img, False, full_tau=True)
     gr = ref.backward(sc, (view, full, proj), cam.tanfovx, cam.tanfovy, bg, r["radii"], ct["color"], ct["depth"], sh=sh,
-                      degree=2, campos=center)
+                      degree=degree, campos=center)
     for n, t in zip(["means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations", "tau"], out):
         if n == "colors":
             continue  # with SH the reference's dL_dcolors is an internal buffer
         assert _relmax(t, gr[n]) < GRAD_REL_TO_MAX, n
+    if degree != 2:
+        return
     # cov3D_precomp: feed the reference's own cov3D (scale_modifier already applied)
     cov = r["cov3D"].clone()
     R2, color2, radii2, *_ = _mine_forward(cam, sc, mats, W, H, bg, cov3D=cov)

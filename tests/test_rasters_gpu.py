@@ -93,32 +93,77 @@ def test_forward_bitexact_and_backward(P, W, H, seed, cfg):
     # The reference accumulates with per-thread float atomics (RS backward.cu:767-911), so its own
     # gradients vary run to run.  The blend-level sums (means2D, colors, opacity) are well conditioned and
     # must agree to 1e-3 of the tensor max on EVERY row.  The per-surfel chain behind them (conic ->
-    # cov2D -> cov3D -> scale/rotation, mean, pose) divides by det^2 of the projected covariance: for a
-    # thin surfel seen edge-on with a radius of hundreds of pixels the reference disagrees with ITSELF by
-    # up to 4e-2 of the tensor max between runs (tools/dev_check_rasters.py), so those tensors are held
-    # to: >= 99 % of the visible rows within 1e-2 relative (row-wise, floor 1e-3 of the tensor max),
-    # and no row off by more than max(5 %, 10x the reference's own spread) of the tensor max.
-    # The spread is taken over 6 reference runs: with 3 it came out anywhere between 0.3 % and 3 % of
-    # the tensor max on the same scene (tools/dev_surfel_grad_spread.py: ref-ref 2-3 %, ours-ours 0.01 %,
-    # ours-ref 8-12 % on the single worst row of `scales`), which made the bar itself a coin toss.
+    # cov2D -> cov3D -> scale/rotation, mean, pose) cancels catastrophically in fp32 (a*c - b*b of the
+    # projected covariance) for thin surfels seen edge-on, in the reference exactly as here: both are the same
+    # fp32 formulas.  Who is right is decided by the fp64 arbiter (oracle/cpu_rasters64.c: blend + chain in
+    # double on the same tile lists, itself pinned by finite differences in tests/test_oracle_rasters64.py):
+    #   (a) per tensor, max-norm: |ours - fp64| <= 1.5 x max over 6 reference runs of |ref - fp64| (+2e-4)
+    #   (b) chain alone (each side's own fp32 blend sums through the fp64 chain): same bar
+    #   (c) rows with kappa = ac/(ac-b^2) < 10 (85 % of the rows): 99 % of them within 1e-3 of the fp64 row
+    #   (d) summed pose gradient: |ours - fp64| <= max(1.5 x worst reference run, 5e-4)
+    # At the full C3 size the fp64 blend would take minutes on the CPU, so (b) and (c) run against the fp64
+    # chain of our own blend sums and the reference comparison keeps the run-to-run-spread bar.
     runs = [g] + [ref.backward(sc, (view, full, proj), cam.tanfovx, cam.tanfovy, bg, ex["prcppoint"], ex["patch_bbox"],
                                config, r["radii"], ct["color"], ct["normal"], ct["depth"], ct["opac"], campos=center)
                   for _ in range(5)]
     names = ["means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations", "tau"]
+    ours = dict(zip(names, out))
     nvis = int((radii > 0).sum())
-    for n, t in zip(names, out):
-        if n == "sh":
-            continue
-        refs = torch.stack([x[n].double().reshape(P, -1) for x in runs])
-        mx = refs[0].abs().max() + 1e-30
-        err = (t.double().reshape(P, -1) - refs[0]).abs().max(1).values
-        if n in ("means2D", "colors", "opacity"):
-            assert float(err.max() / mx) < GRAD_REL_TO_MAX, (n, float(err.max() / mx))
-            continue
-        spread = float((refs.max(0).values - refs.min(0).values).max() / mx)
-        rel = err / (refs[0].abs().max(1).values + 1e-3 * mx)
-        assert int((rel > 1e-2).sum()) <= max(2, nvis // 100), (n, int((rel > 1e-2).sum()), nvis)
-        assert float(err.max() / mx) < max(0.05, 10 * spread), (n, float(err.max() / mx), spread)
+    for n in ("means2D", "colors", "opacity"):
+        refs0 = runs[0][n].double().reshape(P, -1)
+        mx = refs0.abs().max() + 1e-30
+        err = (ours[n].double().reshape(P, -1) - refs0).abs().max(1).values
+        assert float(err.max() / mx) < GRAD_REL_TO_MAX, (n, float(err.max() / mx))
+    from oracle import cpu_rasters64 as O64
+    chain_names = ("means3D", "cov3D", "scales", "rotations", "tau")
+    bs = {k: v.clone() for k, v in RC.debug_blend_sums(1, P, geom).items()}
+    mats3 = (view, full, proj)
+    own64 = O64.chain(sc, mats3, W, H, cam.tanfovx, cam.tanfovy, config, radii, ours["means2D"], bs["conic"],
+                      bs["normal"], bs["depths"])
+    co = dv["records"][:, 1, :3].double().cpu()
+    kappa = (co[:, 0] * co[:, 2]) / (co[:, 0] * co[:, 2] - co[:, 1] ** 2).clamp_min(1e-300)
+    easy = (radii.cpu() > 0) & (kappa < 10)
+    assert int(easy.sum()) > nvis // 2
+
+    def relmax(a, b):
+        b = b.double().cpu().reshape(P, -1)
+        return float((a.double().cpu().reshape(P, -1) - b).abs().max() / (b.abs().max() + 1e-300))
+
+    def rowrel(a, b):
+        a, b = a.double().cpu().reshape(P, -1), b.double().cpu().reshape(P, -1)
+        return (a - b).abs().max(1).values / (b.abs().max(1).values + 1e-4 * b.abs().max())
+
+    if P <= 50000:
+        a64 = O64.blend(sc, mats3, W, H, cam.tanfovx, cam.tanfovy, bg, config, radii, dv["point_list"], dv["ranges"], ct)
+        for k, img_ in dict(color=color, normal=normal, depth=depth, opac=opac).items():   # fp64 decisions flip a few pixels
+            d = (img_.double().cpu() - a64[k].reshape(img_.shape)).abs()
+            assert float(d.flatten().quantile(0.999)) <= 1e-4 * float(a64[k].abs().max()) + 1e-6, k
+        g64 = O64.chain(sc, mats3, W, H, cam.tanfovx, cam.tanfovy, config, radii, a64["g_means2D"], a64["g_conic"],
+                        a64["g_normal"], a64["g_depths"])
+        for n in chain_names:
+            e_ours = relmax(ours[n], g64[n])
+            e_ref = max(relmax(x[n], g64[n]) for x in runs)
+            assert e_ours <= 1.5 * e_ref + 2e-4, ("vs fp64 arbiter", n, e_ours, e_ref)
+            x0 = runs[0]
+            ref_own = O64.chain(sc, mats3, W, H, cam.tanfovx, cam.tanfovy, config, radii, x0["means2D"],
+                                x0["conic"].reshape(P, 4)[:, [0, 1, 3]], x0["normal"], x0["depths"])
+            c_ours, c_ref = relmax(ours[n], own64[n]), relmax(x0[n], ref_own[n])
+            assert c_ours <= 1.5 * c_ref + 2e-4, ("chain alone", n, c_ours, c_ref)
+            assert float(rowrel(ours[n], g64[n])[easy].quantile(0.99)) < 1e-3, ("well-conditioned rows", n)
+        tau64 = g64["tau"].sum(0)
+        t_ours = float((ours["tau"].double().sum(0).cpu() - tau64).abs().max() / tau64.abs().max())
+        t_ref = max(float((x["tau"].double().sum(0).cpu() - tau64).abs().max() / tau64.abs().max()) for x in runs)
+        assert t_ours <= max(1.5 * t_ref, 5e-4), ("pose gradient vs fp64", t_ours, t_ref)
+    else:
+        for n in chain_names:
+            assert float(rowrel(ours[n], own64[n])[easy].quantile(0.99)) < 1e-3, ("well-conditioned rows (chain)", n)
+            refs = torch.stack([x[n].double().reshape(P, -1) for x in runs])
+            mx = refs[0].abs().max() + 1e-30
+            err = (ours[n].double().reshape(P, -1) - refs[0]).abs().max(1).values
+            spread = float((refs.max(0).values - refs.min(0).values).max() / mx)
+            rel = err / (refs[0].abs().max(1).values + 1e-3 * mx)
+            assert int((rel > 1e-2).sum()) <= max(2, nvis // 100), (n, int((rel > 1e-2).sum()), nvis)
+            assert float(err.max() / mx) < max(0.05, 10 * spread), (n, float(err.max() / mx), spread)
     if CONFIGS[cfg][0]:
         assert float(out[6][:, 2].abs().max()) == 0.0  # dL_dscale.z = 0 for surfaces (RS backward.cu:419)
     out2 = RC.rasterize_gaussians_surfel_backward(

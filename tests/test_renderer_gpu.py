@@ -137,3 +137,91 @@ def test_render_contract(gs_type):
     # flip on isolated pixels, everything else must agree
     diff = (res2["render"] - res["render"].detach()).abs()
     assert float((diff > 1e-3).float().mean()) < 1e-3 and float(diff.max()) < 5e-2
+
+
+# ---- numeric parity of everything render() does AROUND the rasterizer ---------------------------------------
+# tests/golden/render_post.npz was produced by the REFERENCE render() (GR:27-466) over the recording stand-in
+# of tests/fake_raster.py (tests/golden/make_render_golden.py); the mirror runs over the same stand-in.
+RGOLD = os.path.join(os.path.dirname(__file__), "golden", "render_post.npz")
+
+
+@pytest.mark.parametrize("case", ["surfel", "surfel_down", "gs3d"])
+def test_render_postprocessing_matches_reference_golden(case, monkeypatch):
+    import math as m
+    import sys
+    sys.path.insert(0, os.path.dirname(__file__))
+    import fake_raster as FR
+    from pings_b200 import gaussian_renderer as GRM
+    from pings_b200.decoder import Decoder
+    from pings_b200.neural_points import default_config
+    z = np.load(RGOLD)
+    p = case + "."
+    N, Fg, Fc, Hd, Lv, K, down, d2n, affine, surround, seed = [int(x) for x in z[p + "meta"]]
+    dev = "cuda"
+    cfg = default_config(device=dev)
+    decs = {"gauss_xyz": Decoder(cfg, Fg, Hd, Lv, 3, K, 0), "gauss_rot": Decoder(cfg, Fg, Hd, Lv, 4, K, 0),
+            "gauss_scale": Decoder(cfg, Fg, Hd, Lv, 3, K, 0), "gauss_alpha": Decoder(cfg, Fg, Hd, Lv, 1, K, 0),
+            "gauss_color": Decoder(cfg, Fc, Hd, Lv, 3, K, 3)}
+    for name, d in decs.items():
+        pre = f"{p}dec.{name}."
+        d.load_state_dict({k[len(pre):]: torch.from_numpy(z[k]) for k in z.files if k.startswith(pre)})
+        d.to(dev)
+    data = {k[len(p) + 5:]: torch.from_numpy(z[k]).to(dev) for k in z.files if k.startswith(p + "data.")}
+    data["resolution"] = 0.25
+    gaussians = None
+    if surround:
+        gaussians = {k[len(p) + 4:]: torch.from_numpy(z[k]).to(dev) for k in z.files if k.startswith(p + "sur.")}
+    W, H, fx = 96, 64, 80.0
+    T_wc = torch.eye(4)
+    T_wc[:3, 3] = torch.tensor([0.3, -0.2, 0.1])
+    wvt = torch.linalg.inv(T_wc).T.contiguous().to(dev)
+    proj = torch.eye(4, device=dev)
+    cam = _Cam(device=torch.device(dev), uid=0, image_width=W, image_height=H, FoVx=2 * m.atan(W / (2 * fx)),
+               FoVy=2 * m.atan(H / (2 * fx)), zfar=100.0, fx=fx, fy=fx,
+               prcppoint=torch.from_numpy(z[p + "cam.prcppoint"]).to(dev), projection_matrix=proj,
+               world_view_transform=wvt, full_proj_transform=wvt @ proj, camera_center=T_wc[:3, 3].to(dev),
+               cam_rot_delta=torch.zeros(3, device=dev), cam_trans_delta=torch.zeros(3, device=dev),
+               exposure_mat=torch.from_numpy(z[p + "cam.exposure_mat"]).to(dev),
+               exposure_offset=torch.from_numpy(z[p + "cam.exposure_offset"]).to(dev),
+               exposure_a=torch.from_numpy(z[p + "cam.exposure_a"]).to(dev),
+               exposure_b=torch.from_numpy(z[p + "cam.exposure_b"]).to(dev))
+    surfel = case != "gs3d"
+    log = {}
+    fake = FR.make_fake(surfel, torch.from_numpy(z[p + "visible"]), seed, log)
+    if surfel:
+        import pings_b200.diff_gaussian_surfel_rasterization as pkg
+    else:
+        import pings_b200.diff_gaussian_rasterization as pkg
+    monkeypatch.setattr(pkg, "GaussianRasterizer", fake)
+    res = GRM.render(cam, None, data, decs, gaussians, torch.tensor([0.1, 0.2, 0.3], device=dev), down_rate=down,
+                     view_concat_on=True, correct_exposure=True, correct_exposure_affine=bool(affine),
+                     learn_color_residual=True, front_only_on=(case != "surfel_down"), d2n_on=bool(d2n),
+                     gs_type="gaussian_surfel" if surfel else "3d_gs")
+    # what reached the rasterizer: settings (q20: full-resolution tanfov, truncated H/W), config, bbox, inputs
+    s = log["settings"]
+    hw = z[p + "settings.hw_tan"]
+    assert (s.image_height, s.image_width) == (int(hw[0]), int(hw[1]))
+    assert abs(s.tanfovx - hw[2]) < 1e-12 and abs(s.tanfovy - hw[3]) < 1e-12 and s.scale_modifier == hw[4]
+    if surfel:
+        assert np.array_equal(s.config.cpu().numpy(), z[p + "settings.config"])
+        assert np.array_equal(s.patch_bbox.cpu().numpy(), z[p + "settings.patch_bbox"])
+    assert log["inputs"]["means3D"].shape[0] == int(z[p + "in.P"][0])      # same alpha > 0 selection + concat
+    torch.testing.assert_close(log["inputs"]["means3D"].detach().cpu(), torch.from_numpy(z[p + "in.means3D"]), rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(log["inputs"]["opacities"].detach().cpu(), torch.from_numpy(z[p + "in.opacities"]), rtol=1e-4, atol=1e-5)
+    # the result dict
+    assert sorted(res.keys()) == list(z[p + "res.keys"])
+    assert sorted(k for k, v in res.items() if v is None) == sorted(z[p + "res.none_keys"].tolist())
+    assert abs(res["visible_neural_point_ratio"] - float(z[p + "res.visible_ratio"][0])) < 1e-12
+    for k in ("render", "surf_depth", "rend_alpha", "rend_normal", "surf_normal", "contributions"):
+        key = p + "res." + k
+        if key in z.files:
+            torch.testing.assert_close(res[k].detach().cpu(), torch.from_numpy(z[key]), rtol=1e-5, atol=1e-6)
+    for k in ("visibility_filter", "radii"):
+        assert np.array_equal(res[k].cpu().numpy(), z[p + "res." + k])
+    # backward of the post-processing: gradient of the fixed loss w.r.t. the rasterizer outputs
+    loss = FR.render_loss(res, seed)
+    assert abs(float(loss) - float(z[p + "loss"][0])) <= 1e-5 * abs(float(z[p + "loss"][0])) + 1e-4
+    loss.backward()
+    for k, leaf in log["leaves"].items():
+        ref = torch.from_numpy(z[p + "grad." + k])
+        torch.testing.assert_close(leaf.grad.cpu(), ref, rtol=1e-4, atol=1e-6 * float(ref.abs().max()) + 1e-7)
