@@ -32,17 +32,24 @@ class _MlpFn(torch.autograd.Function):
                                        torch.cuda.current_stream(dev).cuda_stream), "mlp forward")
         if need:
             ctx.dec, ctx.lead = dec, lead
-            ctx.save_for_backward(x2, hs)
+            # the weights used by THIS forward go through save_for_backward: an optimizer step between forward
+            # and backward then trips autograd's version check instead of silently differentiating against
+            # different weights (eager torch in the reference raises the same error)
+            ctx.save_for_backward(x2, hs, *params)
         return y.reshape(*lead, dec.mlp_out_dim)
 
     @staticmethod
+    @torch.autograd.function.once_differentiable
     def backward(ctx, dy):
+        # once_differentiable: the kernels are opaque to autograd, so a create_graph=True pass through this node
+        # (the reference's analytic eikonal path, utils/tools.py:409-415 with numerical_grad_on=False) raises
+        # instead of silently dropping the second-order term; the default numerical-gradient path is unaffected.
         lib = L.lib()
         dec = ctx.dec
-        x2, hs = ctx.saved_tensors
+        x2, hs, *saved = ctx.saved_tensors
         N, dev = x2.shape[0], x2.device
         dy2 = dy.reshape(N, dec.mlp_out_dim).to(torch.float32).contiguous()
-        mlp, keep = dec._mlp_struct()
+        mlp, keep = dec._mlp_struct(saved)
         lin = dec._linears()
         dWs = [torch.zeros_like(l.weight, dtype=torch.float32) for l in lin]
         dBs = [torch.zeros_like(l.bias, dtype=torch.float32) if l.bias is not None else None for l in lin]
@@ -103,17 +110,20 @@ class Decoder(nn.Module):
     def _linears(self):
         return list(self.layers) + [self.lout]
 
-    def _mlp_struct(self):
+    def _mlp_struct(self, params=None):
+        """PgMlp over the live parameters, or over `params` (weights/biases in _params() order, e.g. the tensors
+        a forward saved for its backward)."""
         m = L.PgMlp()
         m.in_dim, m.hidden_dim, m.hidden_level, m.out_dim = self.input_dim, self.hidden_dim, self.hidden_level, self.mlp_out_dim
         m.leaky_relu = int(bool(self.use_leaky_relu))
         keep = []
+        it = iter(params) if params is not None else None
         for i, lin in enumerate(self._linears()):
-            w = lin.weight.detach().contiguous()
+            w = (next(it) if it is not None else lin.weight).detach().contiguous()
             keep.append(w)
             m.weights[i] = w.data_ptr()
             if lin.bias is not None:
-                b = lin.bias.detach().contiguous()
+                b = (next(it) if it is not None else lin.bias).detach().contiguous()
                 keep.append(b)
                 m.biases[i] = b.data_ptr()
         self._keep = keep

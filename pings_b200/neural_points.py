@@ -52,7 +52,15 @@ class _QueryFeature(torch.autograd.Function):
         out = npm._query_forward(query_points, geo_table, color_table, flags)
         geo_vec, color_vec, weight, nn_counts, certainty, knn_idx, knn_d = out
         ctx.npm, ctx.flags = npm, flags
-        ctx.save_for_backward(query_points, knn_idx, knn_d, weight, nn_counts)
+        # the tables and the point/orientation arrays read by THIS forward are saved, so the backward differentiates
+        # against them even if reset_local_map() / assign_local_to_global() re-binds the attributes in between, and
+        # an in-place edit trips autograd's version check (as eager torch would in the reference)
+        local = flags["query_locally"]
+        pts = npm.local_neural_points if local else npm.neural_points
+        quat = npm.local_point_orientations if local else npm.point_orientations
+        e0 = query_points.new_empty(0)
+        ctx.save_for_backward(query_points, knn_idx, knn_d, weight, nn_counts, pts, quat,
+                              geo_table if geo_table is not None else e0, color_table if color_table is not None else e0)
         ctx.shapes = (None if geo_table is None else geo_table.shape, None if color_table is None else color_table.shape)
         ctx.mark_non_differentiable(nn_counts, certainty, knn_idx)
         e = query_points.new_empty(0)
@@ -60,13 +68,16 @@ class _QueryFeature(torch.autograd.Function):
                 certainty, knn_idx)
 
     @staticmethod
+    @torch.autograd.function.once_differentiable   # opaque kernels: a create_graph=True pass raises (see decoder._MlpFn)
     def backward(ctx, d_geo, d_color, d_weight, *_):
-        query_points, knn_idx, knn_d, weight, nn_counts = ctx.saved_tensors
+        query_points, knn_idx, knn_d, weight, nn_counts, pts, quat, geo_t, color_t = ctx.saved_tensors
         gshape, cshape = ctx.shapes
         dq, dg, dc = ctx.npm._query_backward(query_points, knn_idx, knn_d, weight, nn_counts,
                                              d_geo if gshape is not None else None,
                                              d_color if cshape is not None else None, d_weight, gshape, cshape,
-                                             ctx.flags, ctx.needs_input_grad[1])
+                                             ctx.flags, ctx.needs_input_grad[1],
+                                             saved=(pts, quat, geo_t if gshape is not None else None,
+                                                    color_t if cshape is not None else None))
         return None, dq, dg, dc, None
 
 
@@ -248,16 +259,24 @@ class NeuralPoints(nn.Module):
         return geo_vec, color_vec, weight, nn_counts, certainty, knn_idx, knn_d
 
     def _query_backward(self, q, knn_idx, knn_d, weight, nn_counts, d_geo, d_color, d_weight, gshape, cshape, flags,
-                        need_dq):
+                        need_dq, saved=None):
         lib = L.lib()
         dev = q.device
         N = q.shape[0]
         qc = q.detach().to(torch.float32).contiguous()
-        geo_table = self.local_geo_features if flags["query_locally"] else self.geo_features
-        color_table = self.local_color_features if flags["query_locally"] else self.color_features
-        geo_table = geo_table.detach() if gshape is not None else None
-        color_table = color_table.detach() if cshape is not None else None
+        if saved is not None:
+            pts, quat, geo_table, color_table = saved
+            geo_table = geo_table.detach() if geo_table is not None else None
+            color_table = color_table.detach() if color_table is not None else None
+        else:
+            pts = quat = None
+            geo_table = self.local_geo_features if flags["query_locally"] else self.geo_features
+            color_table = self.local_color_features if flags["query_locally"] else self.color_features
+            geo_table = geo_table.detach() if gshape is not None else None
+            color_table = color_table.detach() if cshape is not None else None
         a = self._query_struct(flags, geo_table, color_table)
+        if pts is not None:   # the arrays the forward read (see _QueryFeature.forward)
+            a.points, a.orientations = L.ptr(pts), L.ptr(quat)
         dq = torch.zeros(N, 3, dtype=torch.float32, device=dev) if need_dq else None
         dg = torch.zeros(gshape, dtype=torch.float32, device=dev) if gshape is not None else None
         dc = torch.zeros(cshape, dtype=torch.float32, device=dev) if cshape is not None else None

@@ -50,6 +50,10 @@ class FlatGradAllReduce:
         if not self.params:
             raise ValueError("FlatGradAllReduce: no parameters")
         dev, dt = self.params[0].device, self.params[0].dtype
+        for p in self.params:
+            if p.device != dev or p.dtype != dt:
+                raise ValueError("FlatGradAllReduce: all parameters must share one device and dtype "
+                                 f"(got {p.device}/{p.dtype} next to {dev}/{dt})")
         self.sizes = [p.numel() for p in self.params]
         self.flat = torch.zeros(sum(self.sizes), dtype=dt, device=dev)
         self.views = list(self.flat.split(self.sizes))
@@ -62,7 +66,13 @@ class FlatGradAllReduce:
         """Make every `p.grad` a view of the flat buffer and zero it: autograd then accumulates straight into
         the buffer (AccumulateGrad adds in place into an existing .grad), so `launch()` / `wait()` need no
         pack / scatter copies (2 copies per parameter per step otherwise).  Call once per step INSTEAD of
-        setting the grads to None; a caller that replaces `p.grad` afterwards simply falls back to the copies."""
+        setting the grads to None; a caller that replaces `p.grad` afterwards simply falls back to the copies.
+
+        Not combinable with side_stream=True: the collective would then reduce the very buffer that any backward
+        work still running after launch() accumulates into (a data race), so that combination raises."""
+        if self.stream is not None:
+            raise RuntimeError("FlatGradAllReduce.attach() cannot be used with side_stream=True: gradients would "
+                               "accumulate into the buffer while it is being reduced")
         self.flat.zero_()
         for p, v in zip(self.params, self.views):
             p.grad = v.view(p.shape)
