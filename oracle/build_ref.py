@@ -65,6 +65,34 @@ def _build_ssim() -> str | None:
     return target
 
 
+PY_STAGE = ["model/__init__.py", "model/neural_gaussians.py", "model/decoder.py", "utils/__init__.py", "utils/config.py",
+            "utils/tools.py", "utils/campose_utils.py", "config/run_pin_slam.yaml", "config/run_kitti_gs.yaml"]
+
+
+def _stage_python() -> str | None:
+    """Stage the reference's own PyTorch neural-point / decoder modules into oracle/_ref/py/ (git-ignored, travels
+    with the gpurun snapshot like the built .so files) so that bench.py can time the REFERENCE's CPU SDF path on the
+    GPU box's host cores (`cpu_baseline.kind = "reference"`, BASELINE.json north_star).  Files are copied verbatim;
+    nothing under oracle/_ref/ enters the repository history."""
+    import shutil
+    dst_root = os.path.join(OUT, "py")
+    n = 0
+    for rel in PY_STAGE:
+        src = os.path.join(REF, rel)
+        if not os.path.exists(src):
+            continue
+        dst = os.path.join(dst_root, rel)
+        os.makedirs(os.path.dirname(dst), exist_ok=True)
+        if not os.path.exists(dst) or os.path.getmtime(dst) < os.path.getmtime(src):
+            shutil.copy2(src, dst)
+        n += 1
+    for pkg in ("model", "utils"):
+        init = os.path.join(dst_root, pkg, "__init__.py")
+        if os.path.isdir(os.path.dirname(init)) and not os.path.exists(init):
+            open(init, "w").close()
+    return dst_root if n else None
+
+
 def build(verbose: bool = True) -> dict[str, str | None]:
     if not os.path.isdir(REF):
         if verbose:
@@ -77,6 +105,7 @@ def build(verbose: bool = True) -> dict[str, str | None]:
     if os.path.exists(os.path.join(HERE, "ref_rs_capi.cu")):
         res["ref_rs"] = _build_raster("ref_rs", "diff-gaussian-surfel-rasterization-w-pose", "ref_rs_capi.cu")
     res["ref_ssim"] = _build_ssim()
+    res["ref_python"] = _stage_python()
     if verbose:
         for k, v in res.items():
             print(f"[oracle] {k}: {v}")

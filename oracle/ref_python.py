@@ -11,15 +11,25 @@ import sys
 from unittest.mock import MagicMock
 
 REF = os.environ.get("PINGS_REFERENCE", "/root/reference")
+if not os.path.isdir(os.path.join(REF, "model")):
+    # the GPU box has no /root/reference: use the modules oracle/build_ref.py staged into oracle/_ref/py/
+    _staged = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "py")
+    if os.path.isdir(os.path.join(_staged, "model")):
+        REF = _staged
 
 
 def available() -> bool:
     return os.path.isdir(os.path.join(REF, "model"))
 
 
+def staged_only() -> bool:
+    return REF.endswith(os.path.join("_ref", "py"))
+
+
 def _stub():
     for m in ["open3d", "matplotlib", "matplotlib.cm", "matplotlib.pyplot", "roma", "imageio", "wandb", "natsort",
-              "open3d.visualization", "open3d.visualization.gui", "open3d.visualization.rendering"]:
+              "open3d.visualization", "open3d.visualization.gui", "open3d.visualization.rendering", "pypose", "kornia",
+              "cv2", "plyfile", "rich", "gtsam", "pytorch3d", "skimage", "skimage.metrics", "lpips"]:
         if m not in sys.modules:
             try:
                 __import__(m)

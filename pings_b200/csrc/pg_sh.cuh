@@ -79,6 +79,9 @@ __device__ inline F3 sh_to_rgb_backward(int idx, int deg, int max_coeffs, F3 pos
   F3 dx = {0, 0, 0}, dy = {0, 0, 0}, dz = {0, 0, 0};
   float x = dir.x, y = dir.y, z = dir.z;
   F3* out = reinterpret_cast<F3*>(dL_dshs) + (size_t)idx * max_coeffs;
+  // coefficients above the active degree get no gradient (the reference's dL_dsh is zero-filled,
+  // R3 rasterize_points.cu:166; ours is not pre-zeroed)
+  for (int k = (deg + 1) * (deg + 1); k < max_coeffs; ++k) out[k] = F3{0.f, 0.f, 0.f};
   out[0] = kShC0 * dL_dRGB;
   if (deg > 0) {
     out[1] = (-kShC1 * y) * dL_dRGB;

@@ -172,7 +172,7 @@ def test_query_certainty_matches_reference_golden():
     assert np.array_equal(npm.buffer_pt_index[occ].cpu().numpy(), G["assigned.hash_values"])
     q = torch.from_numpy(G["certainty.q"]).cuda()
     npm.set_search_neighborhood(num_nei_cells=1, search_alpha=0.0)
-    assert npm.neighbor_K == int(G["certainty.K"][0]) == 7
+    assert npm.neighbor_K == int(G["certainty.K"][0]) == 1   # dx^2 < (1 + 0)^2 keeps the query's own voxel only
     c1 = npm.query_certainty(q)
     npm.set_search_neighborhood(num_nei_cells=npm.config.num_nei_cells, search_alpha=npm.config.search_alpha)
     c2 = npm.query_certainty(q)

