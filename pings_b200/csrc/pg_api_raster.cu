@@ -148,7 +148,9 @@ int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, vo
   carve_binning(num_rendered, W, H, binning_ws, &bw);
   carve_image(prm->variant, W, H, image_ws, &iw);
   const uint32_t* point_list = nullptr;
-  {
+  if (band_path(gx, gy) && num_rendered > 0 && P > 0) {
+    PG_CUDA(bin_instances(gw, bw, iw, P, W, H, num_rendered, &point_list, st));   // times each kernel itself
+  } else {
     Phase ph("binning", st);
     PG_CUDA(bin_instances(gw, bw, iw, P, W, H, num_rendered, &point_list, st));
   }

@@ -368,19 +368,38 @@ inline cudaError_t band_bin(const BandWs& w, int P, int gx, int gy, int64_t R, c
   cudaError_t e = cudaMemsetAsync(w.ticket, 0, 2 * sizeof(uint32_t), st);
   if (e != cudaSuccess) return e;
   const int ctasA = nchunks / kBandWarps;
-  band_rows_kernel<false><<<ctasA, kBandWarps * 32, smA, st>>>(P, per_warp, NB, gy, nchunks, sorted_idx, srect, w.matA,
-                                                               nullptr, nullptr);
-  band_list_scan_kernel<<<nL, 256, 0, st>>>(nL, nchunks, w.matA, w.lcount, w.lstart, w.segbase, w.ticket);
-  band_rows_kernel<true><<<ctasA, kBandWarps * 32, smA, st>>>(P, per_warp, NB, gy, nchunks, sorted_idx, srect, w.matA,
-                                                              w.lstart, w.recs);
-  band_expand_kernel<false><<<sms * 8, kBandWarps * 32, smC, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect, w.tilemat,
-                                                                    nullptr, nullptr, nullptr);
+  // one timed phase per kernel (opt-in phase timer): bench.py reports the roofline of a single kernel
+  {
+    Phase ph("band_rows_kernel<count>", st);
+    band_rows_kernel<false><<<ctasA, kBandWarps * 32, smA, st>>>(P, per_warp, NB, gy, nchunks, sorted_idx, srect, w.matA,
+                                                                 nullptr, nullptr);
+  }
+  {
+    Phase ph("band_list_scan_kernel", st);
+    band_list_scan_kernel<<<nL, 256, 0, st>>>(nL, nchunks, w.matA, w.lcount, w.lstart, w.segbase, w.ticket);
+  }
+  {
+    Phase ph("band_rows_kernel<write>", st);
+    band_rows_kernel<true><<<ctasA, kBandWarps * 32, smA, st>>>(P, per_warp, NB, gy, nchunks, sorted_idx, srect, w.matA,
+                                                                w.lstart, w.recs);
+  }
+  {
+    Phase ph("band_expand_kernel<count>", st);
+    band_expand_kernel<false><<<sms * 8, kBandWarps * 32, smC, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect, w.tilemat,
+                                                                      nullptr, nullptr, nullptr);
+  }
   const int slots = nL * kBandTiles;
   const int ctasT = (slots + 7) / 8 < sms * 8 ? (slots + 7) / 8 : sms * 8;
-  band_tile_scan_kernel<<<ctasT, 256, 0, st>>>(nL, NB, gx, T, w.segbase, w.tilemat, w.tiletot, w.tilestart, ranges,
-                                               w.ticket + 1);
-  band_expand_kernel<true><<<sms * 3, kBandWarps * 32, smW, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect, w.tilemat,
-                                                                   w.tiletot, w.tilestart, out);
+  {
+    Phase ph("band_tile_scan_kernel", st);
+    band_tile_scan_kernel<<<ctasT, 256, 0, st>>>(nL, NB, gx, T, w.segbase, w.tilemat, w.tiletot, w.tilestart, ranges,
+                                                 w.ticket + 1);
+  }
+  {
+    Phase ph("band_expand_kernel<write>", st);
+    band_expand_kernel<true><<<sms * 3, kBandWarps * 32, smW, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect, w.tilemat,
+                                                                     w.tiletot, w.tilestart, out);
+  }
   (void)R;
   return cudaGetLastError();
 }

@@ -21,6 +21,12 @@ def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales,
                                      cov3Ds_precomp, theta, rho, raster_settings)
 
 
+# Extension (no reference counterpart): GaussianRasterizer.param_grads_out, a flat fp32 buffer of 14*P elements that
+# the backward writes the Gaussian-parameter gradients into ([means3D | colors | opacity | scales | rotations], the
+# layout of pings_b200.parallel.FlatGradAllReduce), so a data-parallel caller all-reduces it without a gather copy.
+_PENDING: dict = {}
+
+
 class _RasterizeGaussians(torch.autograd.Function):
     """reference: __init__.py:48-171."""
 
@@ -44,6 +50,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer, depth, opacity, n_touched = res
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
+        ctx.param_grads_out = _PENDING.pop("grads_out", None)
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geomBuffer,
                               binningBuffer, imgBuffer)
         ctx.mark_non_differentiable(radii, n_touched)
@@ -67,7 +74,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                 print("\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n")
                 raise ex
         else:
-            res = _C.rasterize_gaussians_backward(*args)
+            res = _C.rasterize_gaussians_backward(*args, param_grads_out=ctx.param_grads_out)
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
          grad_rotations, grad_tau) = res
         # the kernel already reduced dL_dtau over Gaussians ([1,6]); same slicing as the reference
@@ -98,6 +105,7 @@ class GaussianRasterizer(nn.Module):
     def __init__(self, raster_settings):
         super().__init__()
         self.raster_settings = raster_settings
+        self.param_grads_out = None   # optional flat gradient buffer (see _PENDING above)
 
     def markVisible(self, positions):
         with torch.no_grad():
@@ -120,5 +128,7 @@ class GaussianRasterizer(nn.Module):
         cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
         theta = empty if theta is None else theta
         rho = empty if rho is None else rho
+        if self.param_grads_out is not None:
+            _PENDING["grads_out"] = self.param_grads_out
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
                                    cov3D_precomp, theta, rho, rs)

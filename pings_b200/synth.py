@@ -146,3 +146,52 @@ def surfels_in_view(cam: Camera, P: int, seed: int = 1, facing: float = 0.7, **k
     qf = torch.stack([-x, w, z, -y], dim=1)  # q * (0,1,0,0): half turn about the local x axis flips the normal
     sc["rotations"] = torch.where(flip[:, None], qf, q).contiguous()
     return sc
+
+
+# ---- config C5 (BASELINE.json configs[4]): inspect_pings-style large-map render ----------------
+def large_map(P: int = 5_000_000, seed: int = 3) -> dict:
+    """P surfels in a 400 m x 400 m x 20 m slab, street-like: 60 % within 2 m of the ground (normals up, random
+    yaw, slight tilt), 40 % anywhere in the slab with random orientation.  Same dictionary as surfels_in_view."""
+    g = torch.Generator().manual_seed(seed + 5000)
+    n_ground = int(P * 0.6)
+    xy = (torch.rand(P, 2, generator=g) - 0.5) * 400.0
+    z = torch.cat([torch.rand(n_ground, generator=g) * 2.0, torch.rand(P - n_ground, generator=g) * 20.0])
+    means = torch.cat([xy, z[:, None]], 1).contiguous()
+    yaw = torch.rand(n_ground, generator=g) * (2 * math.pi)
+    qg = torch.stack([torch.cos(yaw / 2), 0.05 * torch.randn(n_ground, generator=g),
+                      0.05 * torch.randn(n_ground, generator=g), torch.sin(yaw / 2)], 1)
+    qr = torch.randn(P - n_ground, 4, generator=g)
+    rots = torch.nn.functional.normalize(torch.cat([qg, qr], 0), dim=1).contiguous()
+    scales = torch.exp(torch.rand(P, 3, generator=g) * (math.log(0.4) - math.log(0.05)) + math.log(0.05))
+    scales[:, 2] = 1e-7
+    opac = torch.rand(P, 1, generator=g) * 0.95 + 0.05
+    colors = torch.rand(P, 3, generator=g)
+    perm = torch.randperm(P, generator=g)
+    return dict(means3D=means[perm].contiguous(), scales=scales[perm].contiguous(), rotations=rots[perm].contiguous(),
+                opacities=opac[perm].contiguous(), colors_precomp=colors[perm].contiguous())
+
+
+def loop_cameras(n: int = 64, W: int = 1920, H: int = 1080, radius: float = 100.0, height: float = 1.7) -> list:
+    """n poses on a closed loop (circle of `radius` m, `height` m above the ground), looking along the tangent;
+    camera axes: z forward, x right, y down (cameras.py convention)."""
+    cams = []
+    for i in range(n):
+        phi = 2 * math.pi * i / n
+        c = torch.tensor([radius * math.cos(phi), radius * math.sin(phi), height], dtype=torch.float64)
+        zc = torch.tensor([-math.sin(phi), math.cos(phi), 0.0], dtype=torch.float64)
+        yc = torch.tensor([0.0, 0.0, -1.0], dtype=torch.float64)
+        xc = torch.linalg.cross(yc, zc)
+        T = torch.eye(4, dtype=torch.float64)
+        T[:3, 0], T[:3, 1], T[:3, 2], T[:3, 3] = xc, yc, zc, c
+        cams.append(Camera(W=W, H=H, fx=1000.0 * W / 1920.0, fy=1000.0 * W / 1920.0, cx=W / 2.0, cy=H / 2.0, T_wc=T))
+    return cams
+
+
+def pings_like_gaussians(cam: Camera, P: int = 300_000, seed: int = 7) -> dict:
+    """A second 3DGS scene with PINGS-like occupancy (R/P about 5-15, tile lists that do not saturate
+    after a few percent): spawned-Gaussian sized splats (0.02-0.15 m) on depth shells with low opacity, all inside
+    the frustum - the shape a PINGS mapping frame has (GR:661-685: scales <= voxel size, alpha = tanh(.))."""
+    sc = gaussians_in_view(cam, P, seed, scale_lo=0.02, scale_hi=0.15)
+    g = torch.Generator().manual_seed(seed + 4000)
+    sc["opacities"] = (torch.rand(P, 1, generator=g) * 0.35 + 0.05).contiguous()
+    return sc
