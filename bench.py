@@ -145,25 +145,38 @@ def make_scene(rank: int):
     return cam, sc, ct, target
 
 
-def algorithmic_bytes(P: int, R: int, W: int, H: int, Q: int = -1) -> dict:
-    """Per-launch algorithmic HBM bytes of each phase."""
+def algorithmic_bytes(P: int, R: int, W: int, H: int, Q: int = -1, surfel: bool = False) -> dict:
+    """Per-launch algorithmic HBM bytes of every kernel of a step.  Keys are the
+    phase names the library's phase timer reports (one per kernel for the band binning)."""
     WH = W * H
-    T = ((W + 15) // 16) * ((H + 15) // 16)
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    T = gx * gy
     NC = min(4096, max(148, (4 << 20) // T))   # bin_max_chunks (pg_raster_common.cuh)
-    return {
-        "preprocess_fwd": 104 * P,                    # 44 B in + 60 B out per Gaussian
-        "depth_sort": (4 * (4 + 8 + 8) + 4 + 16 + 12) * P,  # 4 LSD passes over (u32 key, u32 value) + rect gather + weight scan
-        # band binning (DESIGN.md 4.1), Q band records: stage A walks (rect 8 B [+ id 4 B]) per Gaussian twice
-        # and writes 4 B per record; stage B reads each record (4 B + 4 B of its rect) twice and writes one
-        # 4-B id per instance; count matrices (r+w) and ranges.  One-level fallback when Q < 0.
-        "binning": (2 * 8 * P + 4 * P + 4 * Q + 2 * 8 * Q + 4 * R + 3 * 4 * (Q // 4) + 8 * T) if Q >= 0
-                   else 2 * 12 * P + 4 * R + 16 * T * NC + 8 * T,
+    nL = ((gx + 31) // 32) * gy                # (row, band) lists
+    nch = min(4096, max(256, ((1 << 20) // max(nL, 1)) & ~7))   # band_row_chunks
+    out = {
+        "preprocess_fwd": (160 if surfel else 104) * P,      # 44 B in + 60 B out per Gaussian (surfel: + normal, zx, zy)
+        "depth_sort": (4 * (4 + 8 + 8) + 4 + 16 + 12) * P,   # 4 LSD passes over (u32 key, u32 value) + rect gather + weight scan
         # blend kernels: HBM sees the id list once, each record once (re-reads by other tiles hit L2) and the
-        # images; the per-instance record / gradient traffic (L2_BYTES below) is L2 and shared-memory work
-        "render_fwd": 4 * R + 48 * P + 28 * WH,
-        "render_bwd": 4 * R + 48 * P + 2 * 48 * P + 52 * WH,
-        "preprocess_bwd": 190 * P,
+        # images; the per-instance record / gradient traffic (l2_bytes below) is L2 and shared-memory work
+        "render_fwd": 4 * R + (68 if surfel else 48) * P + (44 if surfel else 28) * WH,
+        "render_bwd": 4 * R + (68 if surfel else 48) * P + 2 * (64 if surfel else 48) * P + (68 if surfel else 52) * WH,
+        "preprocess_bwd": (215 if surfel else 190) * P,
     }
+    if Q >= 0:   # band binning (DESIGN.md 4.1), Q band records, S segments of 128 records
+        S = Q // 128 + nL
+        out.update({
+            "band_rows_kernel<count>": 8 * P + 4 * nL * nch,                 # depth-ordered rects in, count matrix out
+            "band_list_scan_kernel": 2 * 4 * nL * nch,
+            "band_rows_kernel<write>": 8 * P + 4 * P + 4 * nL * nch + 4 * Q,  # rect + id in, one 4-B record per (Gaussian, row, band)
+            "band_expand_kernel<count>": 4 * Q + 8 * Q + 4 * 32 * S,          # record + its rect (gather) in, per-tile segment counts out
+            "band_tile_scan_kernel": 2 * 4 * 32 * S + 8 * T,
+            "band_expand_kernel<write>": 4 * Q + 8 * Q + 4 * 32 * S + 4 * R,  # + one 4-B id per instance out
+        })
+        out["binning"] = sum(v for k, v in out.items() if k.startswith("band_"))
+    else:
+        out["binning"] = 2 * 12 * P + 4 * R + 16 * T * NC + 8 * T
+    return out
 
 
 def l2_bytes(P: int, R: int) -> dict:
@@ -173,6 +186,32 @@ def l2_bytes(P: int, R: int) -> dict:
 
 
 BAND_LISTS: dict = {}   # {"n": (row, band) lists of the benchmarked tile grid}
+
+
+def roofline_tables(phase_ms: dict, ab: dict, pk: dict, l2: dict | None = None):
+    """-> (per-kernel table, per-phase table with the band kernels folded into `binning`, name of the longest kernel)."""
+    def row(ms, b):
+        gbs = b / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        return dict(ms=round(ms, 4), alg_bytes=int(b), gbs=round(gbs, 1), frac=round(gbs / pk["hbm_gbs"], 4))
+    per_kernel = {k: row(ms, ab.get(k, 0)) for k, ms in phase_ms.items()}
+    folded: dict = {}
+    for k, ms in phase_ms.items():
+        kk = "binning" if k.startswith("band_") else k
+        folded[kk] = folded.get(kk, 0.0) + ms
+    per_phase = {k: row(ms, ab.get(k, 0)) for k, ms in folded.items()}
+    for k, b in (l2 or {}).items():
+        if k in per_phase:
+            per_phase[k]["l2_bytes"] = b
+            per_phase[k]["l2_gbs"] = round(b / (per_phase[k]["ms"] * 1e-3) / 1e9, 1) if per_phase[k]["ms"] > 0 else 0.0
+    dom = max(phase_ms, key=phase_ms.get)
+    return per_kernel, per_phase, dom
+
+
+# Issue-slot view of the blend kernels (they are not HBM-bound: DRAM < 1 % in ncu): warp instructions executed per
+# launch from the committed ncu --set full capture (profiles/, smsp__inst_executed.sum) over the kernel's duration,
+# against the B200 peak of 148 SMs x 4 schedulers x 1 warp-instruction / clock at the 1.965 GHz maximum SM clock.
+ISSUE_PEAK_GINST = 148 * 4 * 1.965
+ISSUE_ROOFLINE: dict = {}
 
 
 def launches_per_step(T: int, P: int) -> int:
@@ -259,6 +298,8 @@ def run_ours(args, rank, world, local):
     losses: list = []
     rs = GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, bg, 1.0, view, full, proj, 0, center, False, False)
     rast = GaussianRasterizer(rs)
+    if world > 1:
+        rast.param_grads_out = grads_flat
 
     # Double-buffered input staging: the H2D copy of step k+1 runs on a copy stream while step k computes
     # (every copy is inside the timed region; only the first one is exposed).
@@ -296,8 +337,8 @@ def run_ours(args, rank, world, local):
         loss.backward()
         consumed[slot].record(cur)
         if world > 1:
-            torch.cat([leaves[k].grad.flatten() for k in ("means3D", "colors_precomp", "opacities", "scales", "rotations")],
-                      out=grads_flat)
+            # rast.param_grads_out = grads_flat: the backward kernel wrote the parameter gradients straight into
+            # the flat exchange buffer (no pack copy)
             dist.all_reduce(grads_flat)
         res = torch.cat([loss.detach().view(1), rho.grad.flatten(), theta.grad.flatten()])
         host_out[slot].copy_(res, non_blocking=True)
@@ -370,15 +411,8 @@ def run_ours(args, rank, world, local):
     BAND_LISTS["n"] = ((W + 15) // 16 + 31) // 32 * ((H + 15) // 16)
     ab = algorithmic_bytes(P, R, W, H, Q)
     pk = peaks()
-    dom = max(phase_ms, key=phase_ms.get)
-    achieved = ab[dom] / (phase_ms[dom] * 1e-3) / 1e9
-    per_phase = {k: dict(ms=round(phase_ms[k], 4), alg_bytes=ab[k],
-                         gbs=round(ab[k] / (phase_ms[k] * 1e-3) / 1e9, 1),
-                         frac=round(ab[k] / (phase_ms[k] * 1e-3) / 1e9 / pk["hbm_gbs"], 4)) for k in phase_ms}
-    for k, b in l2_bytes(P, R).items():
-        if k in per_phase:
-            per_phase[k]["l2_bytes"] = b
-            per_phase[k]["l2_gbs"] = round(b / (phase_ms[k] * 1e-3) / 1e9, 1)
+    per_kernel, per_phase, dom = roofline_tables(phase_ms, ab, pk, l2_bytes(P, R))
+    achieved = per_kernel[dom]["gbs"]
     T = ((W + 15) // 16) * ((H + 15) // 16)
     line = {
         "metric": "raster fwd+bwd Mpix/s (3DGS, pose grads)", "value": round(value, 2), "unit": "Mpix/s",
@@ -399,7 +433,11 @@ def run_ours(args, rank, world, local):
         "gpu_launches": launches_per_step(T, P) * args.steps,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": round(achieved / pk["hbm_gbs"], 4), "traffic": TRAFFIC.get(dom),
-                     "peak_source": pk["source"], "phases": per_phase},
+                     "peak_source": pk["source"], "kernels": per_kernel, "phases": per_phase,
+                     "issue": ISSUE_ROOFLINE,
+                     "note": "kernel = the single longest kernel of the step (per-kernel CUDA-event pairs on the launching "
+                             "stream, separate pass); `phases` folds the six band-binning kernels into `binning`; the "
+                             "blend kernels are issue-bound (see `issue`), HBM fractions are reported for all"},
     }
     return line
 
@@ -485,7 +523,7 @@ def run_reference(args, rank, world, local):
 
 # ----------------------------------------------------------------------------------------------
 # Second half of the metric: SDF queries/s (config C1: one synthetic 64x1800 scan, PIN-SLAM settings)
-def sdf_leg(args, local, world=1, rank=0) -> dict:
+def sdf_leg(args, local, world=1, rank=0, keep=None) -> dict:
     from pings_b200 import _lib as L, synth_neural as SN
     dev = torch.device("cuda", local)
     npm, dec, q = SN.c1_map_and_queries(device=dev)
@@ -508,6 +546,8 @@ def sdf_leg(args, local, world=1, rank=0) -> dict:
         evs.append((a, b))
     barrier(world)
     ms = sum(a.elapsed_time(b) for a, b in evs) / steps
+    if keep is not None and rank == 0:
+        keep.append((q.clone(), npm.sdf_fused(q, dec)[0].clone()))
     # e2e: host queries -> H2D -> fused query -> D2H of the sdf values
     qh = q.cpu().pin_memory()
     out_h = torch.empty(N, dtype=torch.float32).pin_memory()
@@ -778,11 +818,234 @@ def mapping_leg(args, local, world, rank) -> dict:
                                      "included; host-driven, timed with CUDA events, L2 flushed between steps"}}
 
 
-def sdf_cpu_leg(budget_s: float = 15.0) -> dict:
-    """The reference's PyTorch CPU SDF path restated (oracle/neural_cpu.py) on this box's host cores."""
-    from oracle import neural_cpu as O
+
+# ----------------------------------------------------------------------------------------------
+# Config C5 (BASELINE.json configs[4]; reference caller inspect_pings.py:361 render_with_poses): 5M surfels, 64 novel
+# 1080p views, forward only, views[rank::world], Gaussians replicated - "replicas only", no collective on the path.
+C5 = dict(P=5_000_000, W=1920, H=1080, views=64, seed=3)
+
+
+def _surfel_statics(cam, dev, W, H):
+    view, full, proj, center = [m.to(dev) for m in cam.matrices()]
+    return dict(view=view, full=full, proj=proj, center=center, tanx=cam.tanfovx, tany=cam.tanfovy,
+                prcp=torch.tensor([cam.cx / W, cam.cy / H], device=dev),
+                bbox=torch.tensor([0.0, 0.0, H - 1.0, W - 1.0], device=dev))
+
+
+def large_map_leg(args, local, world, rank) -> dict:
+    from pings_b200 import _lib as L, _raster_c as RC, synth
+    dev = torch.device("cuda", local)
+    P, W, H, NV = C5["P"], C5["W"], C5["H"], C5["views"]
+    sc = {k: v.to(dev) for k, v in synth.large_map(P, C5["seed"]).items()}
+    cams = synth.loop_cameras(NV, W, H)
+    mine = list(range(NV))[rank::world]
+    st = {i: _surfel_statics(cams[i], dev, W, H) for i in mine}
+    cfg = torch.tensor([1, 1, 1, 1, 1], dtype=torch.float32, device=dev)
+    bg = torch.zeros(3, device=dev)
+    e = torch.empty(0)
+
+    def render_view(i):
+        c = st[i]
+        return RC.rasterize_gaussians_surfel(bg, sc["means3D"], sc["colors_precomp"], sc["opacities"], sc["scales"],
+                                             sc["rotations"], 1.0, e, c["view"], c["full"], c["proj"], c["prcp"], c["bbox"],
+                                             c["tanx"], c["tany"], H, W, e, 0, c["center"], False, False, cfg)
+
+    with torch.no_grad():
+        for i in mine[:2]:
+            render_view(i)
+        barrier(world)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        Rs = []
+        for i in mine:      # inputs (280 MB of Gaussians + 150 MB of per-Gaussian state) exceed the 126 MB L2: no flush needed
+            Rs.append(render_view(i)[0])
+        b.record()
+        barrier(world)
+        ms = a.elapsed_time(b)
+        # e2e: the rendered RGB of every view reaches pinned host memory (24.9 MB / view), D2H on a copy stream
+        # overlapping the next view; camera matrices come from the host (tiny H2D)
+        host = [torch.empty(3, H, W, dtype=torch.float32).pin_memory() for _ in range(2)]
+        copy_stream = torch.cuda.Stream(device=dev)
+        done = [torch.cuda.Event() for _ in range(2)]
+        cams_host = {i: [m.pin_memory() for m in cams[i].matrices()] for i in mine}
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for k, i in enumerate(mine):
+            c = st[i]
+            for dst, src in zip((c["view"], c["full"], c["proj"], c["center"]), cams_host[i]):
+                dst.copy_(src, non_blocking=True)
+            out = render_view(i)
+            ev = torch.cuda.Event()
+            ev.record()
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(ev)
+                if k >= 2:
+                    done[k & 1].synchronize()
+                host[k & 1].copy_(out[1], non_blocking=True)
+                out[1].record_stream(copy_stream)
+                done[k & 1].record(copy_stream)
+        copy_stream.synchronize()
+        torch.cuda.synchronize()
+        e2e_ms = (time.perf_counter() - t0) * 1e3
+    t = torch.tensor([ms, e2e_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, e2e_ms = float(t[0]), float(t[1])
+    res = {"metric": "large-map render Mpix/s (5M surfels, 64 novel 1080p views, forward only, C5)",
+           "value": round(NV * W * H / (ms * 1e-3) / 1e6, 2), "unit": "Mpix/s", "ms_per_view": round(ms / len(mine), 4),
+           "views": NV, "views_per_rank": len(mine), "P": P, "W": W, "H": H, "scaling": "strong (64 views split over N)",
+           "num_rendered_mean": int(sum(Rs) / max(len(Rs), 1)),
+           "e2e": {"value": round(NV * W * H / (e2e_ms * 1e-3) / 1e6, 2), "unit": "Mpix/s",
+                   "h2d_bytes_per_view": 4 * (16 * 3 + 3), "d2h_bytes_per_view": 3 * H * W * 4},
+           "l2": "inputs larger than L2 (430 MB of Gaussian data per view)", "collective": "none (replicas only)"}
+    if rank == 0:
+        phases: dict = {}
+        L.timing_enable(True)
+        with torch.no_grad():
+            for i in mine[:3]:
+                out = render_view(i)
+                R = out[0]
+                for name, pms in L.timing_drain():
+                    phases.setdefault(name, []).append(pms)
+        L.timing_enable(False)
+        phase_ms = {k: sum(v) / len(v) for k, v in phases.items()}
+        Q = int(L.lib().pg_raster_band_records(W, H, int(R), out[8].data_ptr(), None))
+        ab = algorithmic_bytes(P, int(R), W, H, Q, surfel=True)
+        ab["depth_sort"] = (4 * (4 + 8 + 8 + 2 * 4) + 4 + 16 + 12) * P    # multi-kernel path: + histogram pass per digit
+        per_kernel, per_phase, dom = roofline_tables(phase_ms, ab, peaks())
+        res["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": per_kernel[dom]["gbs"], "peak": peaks()["hbm_gbs"],
+                           "unit": "GB/s", "frac": per_kernel[dom]["frac"], "kernels": per_kernel, "phases": per_phase,
+                           "band_records": Q}
+    return {"large_map_render": res}
+
+
+# ----------------------------------------------------------------------------------------------
+# A second 3DGS scene with PINGS-like occupancy (the C2 recipe is occlusion-degenerate, every tile list
+# saturates after 2 % of its entries): 300k spawned-Gaussian sized, low-opacity splats, same camera and kernels.
+def raster3_scene_leg(args, local, scene: str = "pings_like") -> dict:
+    from pings_b200 import _lib as L, _raster_c as RC, synth
+    dev = torch.device("cuda", local)
+    W, H = C2["W"], C2["H"]
+    cam = synth.kitti_camera(C2["seed"], W, H)
+    sc_cpu = synth.pings_like_gaussians(cam)
+    P = sc_cpu["means3D"].shape[0]
+    sc = {k: v.to(dev) for k, v in sc_cpu.items()}
+    ct = {k: v.to(dev) for k, v in synth.cotangents(cam, C2["seed"]).items()}
+    view, full, proj, center = [m.to(dev) for m in cam.matrices()]
+    bg = torch.ones(3, device=dev)
+    e = torch.empty(0)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    keep = {}
+
+    def step():
+        R, color, radii, geom, binning, img, depth, opac, n_touched = RC.rasterize_gaussians(
+            bg, sc["means3D"], sc["colors_precomp"], sc["opacities"], sc["scales"], sc["rotations"], 1.0, e, view, full,
+            proj, cam.tanfovx, cam.tanfovy, H, W, e, 0, center, False, False)
+        RC.rasterize_gaussians_backward(bg, sc["means3D"], radii, sc["colors_precomp"], sc["scales"], sc["rotations"], 1.0,
+                                        e, view, full, proj, cam.tanfovx, cam.tanfovy, ct["color"], ct["depth"], e, 0,
+                                        center, geom, R, binning, img, False)
+        keep.update(R=R, geom=geom, binning=binning, img=img, radii=radii)
+        return R
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    steps = max(5, min(args.steps, 20))
+    evs = []
+    for _ in range(steps):
+        flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        R = step()
+        b.record()
+        evs.append((a, b))
+    torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in evs) / steps
+    dv = RC.debug_views(0, P, W, H, R, keep["geom"], keep["binning"], keep["img"])
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    ll = (dv["ranges"][:, 1] - dv["ranges"][:, 0]).float()
+    nc = dv["n_contrib"].float().view(H, W)
+    pad = torch.zeros(((H + 15) // 16) * 16, ((W + 15) // 16) * 16, device=dev)
+    pad[:H, :W] = nc
+    tile_max = pad.view((H + 15) // 16, 16, (W + 15) // 16, 16).amax(dim=(1, 3)).flatten()
+    walked = float((tile_max / ll.clamp_min(1)).mean())
+    phases: dict = {}
+    L.timing_enable(True)
+    for _ in range(3):
+        flush.fill_(1)
+        step()
+        for name, pms in L.timing_drain():
+            phases.setdefault(name, []).append(pms)
+    L.timing_enable(False)
+    phase_ms = {k: round(sum(v) / len(v), 4) for k, v in phases.items()}
+    return {"raster_" + scene: {
+        "metric": "raster fwd+bwd Mpix/s (3DGS, pose grads), PINGS-like occupancy", "value": round(W * H / (ms * 1e-3) / 1e6, 2),
+        "unit": "Mpix/s", "ms_per_step": round(ms, 4), "P": P, "W": W, "H": H, "num_rendered": int(R),
+        "instances_per_gaussian": round(R / max(int((keep["radii"] > 0).sum()), 1), 2),
+        "mean_list_len": round(float(ll.mean()), 1), "fraction_of_list_walked": round(walked, 3),
+        "kernels_ms": phase_ms, "l2": "flushed between steps"}}
+
+
+def sdf_cpu_leg(budget_s: float = 15.0, check_against=None) -> dict:
+    """The REFERENCE's own PyTorch CPU SDF path on this box's host cores (BASELINE.json north_star: "the reference's
+    PyTorch CPU SDF/decoder path ... is the reported baseline"): model/neural_gaussians.py NeuralPoints.update ->
+    query_feature(accumulate_stability=False) + model/decoder.py Decoder.sdf in infer_bs batches under no_grad
+    (utils/mapper.py:2273-2289), imported from /root/reference or, on the GPU box, from the copy oracle/build_ref.py
+    staged under oracle/_ref/py/.  Falls back to the restatement oracle/neural_cpu.py (kind "port") only when neither
+    exists.  check_against: optional (queries, sdf) from the GPU path, compared on the first batch."""
     from pings_b200 import synth_neural as SN
     torch.set_num_threads(os.cpu_count() or 1)
+    from oracle import ref_python as rp
+    if not rp.available():
+        return _sdf_cpu_leg_port(budget_s)
+    cfg = rp.load_config("run_pin_slam.yaml")
+    NP, Dec = rp.neural_points_cls(), rp.decoder_cls()
+    pts = SN.lidar_scan(42, 1800)
+    g = torch.Generator().manual_seed(43)
+    npm = NP(cfg)
+    npm.travel_dist = torch.zeros(1)
+    npm.update(pts, None, None, torch.zeros(3), None, 0)
+    n = npm.neural_points.shape[0]
+    npm.geo_features = 0.1 * torch.randn(n + 1, cfg.feature_dim, generator=g)   # same draw as SN.c1_map_and_queries
+    npm.reset_local_map(torch.zeros(3), None, 0)
+    torch.manual_seed(42)
+    dec = Dec(cfg, cfg.feature_dim, 64, 1, 1)
+    q = (pts + 0.05 * torch.randn(pts.shape, generator=g)).contiguous()
+    bs = int(cfg.infer_bs)
+
+    def run():
+        out = []
+        with torch.no_grad():
+            for h in range(0, q.shape[0], bs):
+                geo, _, w, cnt, _ = npm.query_feature(q[h:h + bs], accumulate_stability=False)
+                out.append(dec.sdf(geo))
+        return torch.cat(out)
+
+    sdf = run()
+    times = []
+    t_end = time.perf_counter() + budget_s
+    while len(times) < 3 or (time.perf_counter() < t_end and len(times) < 20):
+        t0 = time.perf_counter()
+        run()
+        times.append(time.perf_counter() - t0)
+    best, med = min(times), statistics.median(times)
+    res = {"value": round(q.shape[0] / med, 1), "best": round(q.shape[0] / best, 1), "unit": "queries/s",
+           "cores": torch.get_num_threads(), "kind": "reference",
+           "source": "staged copy oracle/_ref/py" if rp.staged_only() else rp.REF,
+           "neural_points": int(n),
+           "sample": f"full C1 scan ({q.shape[0]} queries, infer_bs {bs}, no_grad), reference NeuralPoints.query_feature + "
+                     f"Decoder.sdf, median of {len(times)} runs"}
+    if check_against is not None:
+        qg, sg = check_against
+        if qg.shape == q.shape and bool(torch.equal(qg.cpu(), q)):
+            res["max_abs_diff_vs_gpu"] = float((sg.cpu() - sdf).abs().max())
+    return res
+
+
+def _sdf_cpu_leg_port(budget_s: float = 15.0) -> dict:
+    """Fallback: the restatement oracle/neural_cpu.py (only when no copy of the reference Python is available)."""
+    from oracle import neural_cpu as O
+    from pings_b200 import synth_neural as SN
     npm, dec, q = SN.c1_map_and_queries(device="cpu")
     S = SN.oracle_state(npm)
     Ws = [l.weight.detach() for l in dec._linears()]
@@ -802,6 +1065,122 @@ def sdf_cpu_leg(budget_s: float = 15.0) -> dict:
     return {"value": round(q.shape[0] / med, 1), "best": round(q.shape[0] / best, 1), "unit": "queries/s",
             "cores": torch.get_num_threads(), "kind": "port",
             "sample": f"full C1 scan ({q.shape[0]} queries, infer_bs 80000, no_grad), median of {len(times)} runs"}
+
+
+# ----------------------------------------------------------------------------------------------
+# Reference-arm comparators (bench.py --impl reference): the UNMODIFIED reference CUDA code built into oracle/_ref on
+# the other configurations - R3 on the PINGS-like scene, RS on C3 (fwd+bwd) and C5 (fwd), fused-ssim on the two
+# shapes of FS/tests/test.py:59 and BASELINE.md rows B2/B3.  Same scenes, same L2 flush, device synced wall clock.
+def _timed(fn, steps, flush):
+    fn()
+    torch.cuda.synchronize()
+    ms = 0.0
+    for _ in range(steps):
+        if flush is not None:
+            flush.fill_(1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        fn()
+        torch.cuda.synchronize()
+        ms += (time.perf_counter() - t0) * 1e3
+    return ms / steps
+
+
+def reference_extras(args, local) -> dict:
+    from oracle import ref_api
+    from pings_b200 import synth
+    dev = torch.device("cuda", local)
+    out: dict = {}
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    steps = max(3, min(args.steps, 5))
+    if ref_api.available("ref_r3"):
+        try:
+            W, H = C2["W"], C2["H"]
+            cam = synth.kitti_camera(C2["seed"], W, H)
+            sc = {k: v.to(dev) for k, v in synth.pings_like_gaussians(cam).items()}
+            ct = {k: v.to(dev) for k, v in synth.cotangents(cam, C2["seed"]).items()}
+            view, full, proj, center = [m.to(dev) for m in cam.matrices()]
+            bg = torch.ones(3, device=dev)
+            ref = ref_api.RefRaster3()
+            info = {}
+            def step():
+                r = ref.forward(sc, (view, full, proj), W, H, cam.tanfovx, cam.tanfovy, bg, campos=center, want_views=False)
+                g = ref.backward(sc, (view, full, proj), cam.tanfovx, cam.tanfovy, bg, r["radii"], ct["color"], ct["depth"],
+                                 campos=center)
+                g["tau"].sum(0)
+                info["R"] = r["num_rendered"]
+            ms = _timed(step, steps, flush)
+            out["raster_pings_like"] = {"value": round(W * H / (ms * 1e-3) / 1e6, 2), "unit": "Mpix/s",
+                                        "ms_per_step": round(ms, 4), "num_rendered": int(info["R"]),
+                                        "impl": "reference R3 CUDA (oracle/_ref/libref_r3.so)"}
+        except Exception as ex:
+            out["raster_pings_like"] = f"failed: {ex!r}"
+    if ref_api.available("ref_rs"):
+        try:
+            P, W, H = C3["P"], C3["W"], C3["H"]
+            cam = synth.hd_camera(C3["seed"], W, H)
+            sc = {k: v.to(dev) for k, v in synth.surfels_in_view(cam, P, C3["seed"]).items()}
+            ct = {k: v.to(dev) for k, v in synth.cotangents(cam, C3["seed"], normal=True).items()}
+            s = _surfel_statics(cam, dev, W, H)
+            cfg = torch.tensor([1, 1, 1, 1, 1], dtype=torch.float32, device=dev)
+            bg = torch.zeros(3, device=dev)
+            ref = ref_api.RefRasterS()
+            mats = (s["view"], s["full"], s["proj"])
+            info = {}
+            def step3():
+                r = ref.forward(sc, mats, W, H, s["tanx"], s["tany"], bg, s["prcp"], s["bbox"], cfg, campos=s["center"],
+                                want_views=False)
+                g = ref.backward(sc, mats, s["tanx"], s["tany"], bg, s["prcp"], s["bbox"], cfg, r["radii"], ct["color"],
+                                 ct["normal"], ct["depth"], ct["opac"], campos=s["center"])
+                g["tau"].sum(0)
+                info["R"] = r["num_rendered"]
+            ms = _timed(step3, steps, flush)
+            out["surfel_raster_c3"] = {"value": round(W * H / (ms * 1e-3) / 1e6, 2), "unit": "Mpix/s",
+                                       "ms_per_step": round(ms, 4), "num_rendered": int(info["R"]),
+                                       "note": "rasterizer fwd+bwd only (no loss glue, no SSIM)",
+                                       "impl": "reference RS CUDA (oracle/_ref/libref_rs.so)"}
+            del sc, ct
+        except Exception as ex:
+            out["surfel_raster_c3"] = f"failed: {ex!r}"
+        try:
+            P, W, H = C5["P"], C5["W"], C5["H"]
+            sc = {k: v.to(dev) for k, v in synth.large_map(P, C5["seed"]).items()}
+            cams = synth.loop_cameras(C5["views"], W, H)
+            cfg = torch.tensor([1, 1, 1, 1, 1], dtype=torch.float32, device=dev)
+            bg = torch.zeros(3, device=dev)
+            ref = ref_api.RefRasterS()
+            sub = list(range(0, C5["views"], 8))          # 8 of the 64 views (bounded sample of the same workload)
+            sts = [_surfel_statics(cams[i], dev, W, H) for i in sub]
+            def step5():
+                for s5 in sts:
+                    ref.forward(sc, (s5["view"], s5["full"], s5["proj"]), W, H, s5["tanx"], s5["tany"], bg, s5["prcp"],
+                                s5["bbox"], cfg, campos=s5["center"], want_views=False)
+            ms = _timed(step5, 2, None) / len(sub)
+            out["large_map_render"] = {"value": round(W * H / (ms * 1e-3) / 1e6, 2), "unit": "Mpix/s",
+                                       "ms_per_view": round(ms, 4), "views_timed": len(sub), "P": P,
+                                       "impl": "reference RS CUDA forward (oracle/_ref/libref_rs.so), one GPU"}
+            del sc
+        except Exception as ex:
+            out["large_map_render"] = f"failed: {ex!r}"
+    mod = ref_api.ref_ssim_module()
+    if mod is not None:
+        try:
+            res = {}
+            for shape in ((1, 3, 1080, 1920), (5, 5, 1080, 1920)):
+                g = torch.Generator().manual_seed(9)
+                a = torch.rand(*shape, generator=g).to(dev)
+                b = torch.rand(*shape, generator=g).to(dev)
+                n = a.numel()
+                dmap = torch.full_like(a, 1.0 / n)
+                def ssim_step():
+                    m, d1, d2, d3 = mod.fusedssim(0.01 ** 2, 0.03 ** 2, a, b, True)
+                    mod.fusedssim_backward(0.01 ** 2, 0.03 ** 2, a, b, dmap, d1, d2, d3)
+                ms = _timed(ssim_step, 10, None)
+                res["x".join(map(str, shape))] = {"ms_fwd_bwd": round(ms, 4), "gelem_per_s": round(n / (ms * 1e-3) / 1e9, 2)}
+            out["fused_ssim"] = {"impl": "reference fused-ssim CUDA (oracle/_ref/fused_ssim_cuda_ref.so, --use_fast_math)", **res}
+        except Exception as ex:
+            out["fused_ssim"] = f"failed: {ex!r}"
+    return out
 
 
 # ---- decoder MLP leg (extra.mlp_batch): the one dense contraction of the path ----------------------
@@ -849,6 +1228,32 @@ def mlp_leg(args, local) -> dict:
                      "hbm_gbs": round(byts / ms_tc / 1e6, 1)}}}
 
 
+def _all_ok(ok: bool, world: int, dev) -> bool:
+    """Collective-safe go/no-go: every rank learns whether ALL ranks are fine before entering a leg's collectives."""
+    if world == 1:
+        return ok
+    t = torch.tensor([1 if ok else 0], device=dev, dtype=torch.int32)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(int(t.item()))
+
+
+def run_leg(name, fn, world, dev):
+    """Run an optional leg on every rank.  A rank that fails records the error; the ranks then agree (MIN
+    all-reduce) so that nobody is left waiting inside the leg's next collective, and the leg is reported as failed."""
+    err = None
+    try:
+        res = fn()
+    except Exception as ex:   # noqa: BLE001 - an optional leg must not take the headline down
+        res, err = None, repr(ex)
+    try:
+        ok = _all_ok(err is None, world, dev)
+    except Exception as ex:   # the process group itself is gone
+        ok, err = False, err or repr(ex)
+    if not ok:
+        return {name: f"failed: {err or 'another rank failed'}"}
+    return res
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -856,52 +1261,62 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--legs", default="all", help="comma list of optional legs: sdf,mapping,large_map,surfel,pings_like,mlp")
     args = ap.parse_args()
+    want = (lambda k: True) if args.legs == "all" else (lambda k: k in args.legs.split(","))
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":  # rank 0 alone runs it; no process group is formed
         if int(os.environ.get("RANK", "0")) == 0:
-            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
+            local = int(os.environ.get("LOCAL_RANK", "0"))
+            torch.cuda.set_device(local)
             world = int(os.environ.get("WORLD_SIZE", "1"))
-            ref_line = run_reference(args, 0, world, int(os.environ.get("LOCAL_RANK", "0")))
-            try:  # the reference's CPU SDF path (restated), the reported baseline of the second metric half
-                ref_line.setdefault("extra", {})["sdf"] = sdf_cpu_leg()
-            except Exception as ex:
-                ref_line.setdefault("extra", {})["sdf"] = f"failed: {ex!r}"
+            ref_line = run_reference(args, 0, world, local)
+            ex = ref_line.setdefault("extra", {})
+            ex["note"] = ("the reference is single-GPU (SURVEY.md 0.3): every number of this arm is ONE GPU, whatever "
+                          "n_gpus the job was launched with")
+            if args.legs != "none":
+                try:
+                    ex.update(reference_extras(args, local))
+                except Exception as e:   # noqa: BLE001
+                    ex["comparators"] = f"failed: {e!r}"
+                try:  # the reference's own CPU SDF path, the reported baseline of the second metric half
+                    ex["sdf"] = sdf_cpu_leg()
+                except Exception as e:   # noqa: BLE001
+                    ex["sdf"] = f"failed: {e!r}"
             print(json.dumps(ref_line), flush=True)
         return
     rank, world, local = dist_setup(args.gpus)
+    dev = torch.device("cuda", local)
     line = run_ours(args, rank, world, local)
-    try:  # every rank takes part (query sharding); an optional leg must not take the headline down
-        sdf = sdf_leg(args, local, world, rank)
-    except Exception as ex:
-        sdf = {"sdf": f"failed: {ex!r}"}
-    try:  # C4: every rank renders its view of the batch and joins the gradient exchange
-        mapping = mapping_leg(args, local, world, rank)
-    except Exception as ex:
-        mapping = {"mapping_step": f"failed: {ex!r}"}
+    extra: dict = {}
+    sdf_check: list = []
+    if want("sdf"):
+        extra.update(run_leg("sdf", lambda: sdf_leg(args, local, world, rank, keep=sdf_check), world, dev))
+    if want("mapping"):
+        extra.update(run_leg("mapping_step", lambda: mapping_leg(args, local, world, rank), world, dev))
+    if want("large_map"):
+        extra.update(run_leg("large_map_render", lambda: large_map_leg(args, local, world, rank), world, dev))
     if rank == 0:
-        line.setdefault("extra", {}).update(sdf)
-        line["extra"].update(mapping)
+        line.setdefault("extra", {}).update(extra)
         if world == 1:
-            try:
-                line["extra"].update(surfel_leg(args, local))
-            except Exception as ex:
-                line["extra"]["surfel_ssim"] = f"failed: {ex!r}"
-            try:
-                line["extra"].update(mlp_leg(args, local))
-            except Exception as ex:
-                line["extra"]["mlp_batch"] = f"failed: {ex!r}"
+            for key, name, fn in (("surfel", "surfel_ssim", lambda: surfel_leg(args, local)),
+                                  ("pings_like", "raster_pings_like", lambda: raster3_scene_leg(args, local)),
+                                  ("mlp", "mlp_batch", lambda: mlp_leg(args, local))):
+                if want(key):
+                    line["extra"].update(run_leg(name, fn, 1, dev))
         if world == 1 and not args.no_cpu_baseline:
             cb = cpu_baseline_line(args)
             if cb is not None:
                 line["cpu_baseline"] = cb
             if isinstance(line["extra"].get("sdf"), dict):
-                line["extra"]["sdf"]["cpu_baseline"] = sdf_cpu_leg()
+                try:
+                    line["extra"]["sdf"]["cpu_baseline"] = sdf_cpu_leg(check_against=sdf_check[0] if sdf_check else None)
+                except Exception as e:   # noqa: BLE001
+                    line["extra"]["sdf"]["cpu_baseline"] = f"failed: {e!r}"
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
-
 
 
 if __name__ == "__main__":
