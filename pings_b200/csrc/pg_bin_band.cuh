@@ -25,7 +25,7 @@ constexpr int kBandMaxLists = 1024;   // [row][band] lists; more -> older paths
 constexpr int kBandSegRecs = 128;     // records per warp segment in stage B
 constexpr int kBandStageCap = 2048;   // staged instances per warp (8 KB)
 constexpr int kBandWarps = 8;
-constexpr int kBandStageWords = kBandStageCap + 32;   // staged words + run deltas
+constexpr int kBandStageWords = kBandStageCap + 64;   // staged words + run deltas + the ids of the 32 records in flight
 constexpr int kBandIdBits = 27;       // staged word = owning lane << 27 | Gaussian id  (P < 2^27)
 
 inline int band_count(int gx) { return (gx + kBandTiles - 1) / kBandTiles; }
@@ -62,9 +62,12 @@ struct BandWs {
 // which keeps a list depth-ordered, then the cursors advance cell-parallel.
 template <bool WRITE>
 __global__ void __launch_bounds__(kBandWarps * 32) band_rows_kernel(
-    int P, int per_warp, int NB, int GY, int nchunks, const uint32_t* __restrict__ sorted_idx,
+    int P, const uint32_t* __restrict__ nvalid, int NB, int GY, int nchunks, const uint32_t* __restrict__ sorted_idx,
     const uint2* __restrict__ srect, uint32_t* __restrict__ matA, const uint32_t* __restrict__ lstart,
     uint32_t* __restrict__ recs) {
+  // the depth sort dropped the culled Gaussians: V = *nvalid items, cut into nchunks equal chunks of whole 32-groups
+  P = min(P, (int)*nvalid);
+  const int per_warp = ((P + nchunks - 1) / nchunks + 31) & ~31;
   extern __shared__ uint32_t band_sm[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int chunk = blockIdx.x * kBandWarps + warp;
@@ -189,16 +192,28 @@ __global__ void __launch_bounds__(256) band_list_scan_kernel(int nL, int nchunks
   }
 }
 
-// Lane t appends the ids of the records (one per lane, coverage mask cm) that cover its tile, in lane
-// order, to its run of the stage starting at k; returns the advanced k.
-__device__ __forceinline__ uint32_t band_stage_group(uint32_t cm, uint32_t id, uint32_t lane_bit, int lane,
-                                                     uint32_t* stage, uint32_t k) {
-  const uint32_t tag = (uint32_t)lane << kBandIdBits;
+// Transpose of the 32 x 32 bit matrix held one row per lane (bit j of lane i -> bit i of lane j): 5 butterfly
+// stages.  Turns the per-record coverage masks (record = lane, bit = tile) into per-tile record masks
+// (tile = lane, bit = record), so that a lane counts with one POPC and walks only the records that cover its tile.
+__device__ __forceinline__ uint32_t band_transpose32(uint32_t v, int lane) {
 #pragma unroll
-  for (int jj = 0; jj < 32; ++jj) {
-    const bool hit = (__shfl_sync(0xffffffffu, cm, jj) & lane_bit) != 0u;
-    const uint32_t idj = __shfl_sync(0xffffffffu, id, jj) | tag;
-    if (hit) stage[k++] = idj;
+  for (int s = 16; s >= 1; s >>= 1) {
+    const uint32_t mask = s == 16 ? 0x0000ffffu : s == 8 ? 0x00ff00ffu : s == 4 ? 0x0f0f0f0fu : s == 2 ? 0x33333333u : 0x55555555u;
+    const uint32_t other = __shfl_xor_sync(0xffffffffu, v, s);
+    v = (lane & s) ? ((v & ~mask) | ((other >> s) & mask)) : ((v & mask) | ((other << s) & ~mask));
+  }
+  return v;
+}
+
+// Lane t appends the ids of the records that cover its tile (col = mask over the 32 records in flight, ids staged
+// in shared memory by the caller), in record order, to its run of the stage starting at k; returns the advanced k.
+__device__ __forceinline__ uint32_t band_stage_group(uint32_t col, const uint32_t* ids, int lane, uint32_t* stage,
+                                                     uint32_t k) {
+  const uint32_t tag = (uint32_t)lane << kBandIdBits;
+  while (col) {
+    const int j = __ffs(col) - 1;
+    col &= col - 1;
+    stage[k++] = ids[j] | tag;
   }
   return k;
 }
@@ -228,6 +243,7 @@ __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
   // WRITE only: per warp [cap] staged words, [32] run deltas
   uint32_t* stage = band_sm + sb_words + warp * kBandStageWords;
   uint32_t* stage_delta = stage + kBandStageCap;
+  uint32_t* ids = stage_delta + 32;
   for (int k = threadIdx.x; k <= nL; k += blockDim.x) sb[k] = segbase[k];
   __syncthreads();
   const uint32_t S = sb[nL];
@@ -254,7 +270,6 @@ __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
       staged = __shfl_sync(0xffffffffu, inc, 31) <= (uint32_t)kBandStageCap;
       k = staged ? start : 0u;
     }
-    const uint32_t lane_bit = 1u << lane;
     for (uint32_t j0 = 0; j0 < n; j0 += 32) {
       uint32_t id = 0, cm = 0;   // cm = coverage mask of this lane's record over the band's 32 tiles
       if (j0 + lane < n) {
@@ -264,21 +279,24 @@ __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
         const uint32_t x1 = min(rx >> 16, band0 + kBandTiles) - band0;   // 1..32
         cm = (0xffffffffu >> (32u - (x1 - x0))) << x0;
       }
+      const uint32_t col = band_transpose32(cm, lane);   // records (bits) covering this lane's tile
       if (!WRITE) {
-#pragma unroll
-        for (int jj = 0; jj < 32; ++jj) c += (__shfl_sync(0xffffffffu, cm, jj) & lane_bit) ? 1u : 0u;
-      } else if (staged) {
-        k = band_stage_group(cm, id, lane_bit, lane, stage, k);
+        c += __popc(col);
       } else {
-        // dense segment (> cap instances): stage and flush these 32 records on their own (<= 1024 instances)
-        uint32_t cg = 0;
-#pragma unroll
-        for (int jj = 0; jj < 32; ++jj) cg += (__shfl_sync(0xffffffffu, cm, jj) & lane_bit) ? 1u : 0u;
-        const uint32_t inc = warp_incl_scan(cg, lane);
-        band_stage_group(cm, id, lane_bit, lane, stage, inc - cg);
-        stage_delta[lane] = goff + k - (inc - cg);   // k = instances of this tile already written
-        band_flush(stage, stage_delta, __shfl_sync(0xffffffffu, inc, 31), lane, out);
-        k += cg;
+        ids[lane] = id;
+        __syncwarp();
+        if (staged) {
+          k = band_stage_group(col, ids, lane, stage, k);
+        } else {
+          // dense segment (> cap instances): stage and flush these 32 records on their own (<= 1024 instances)
+          const uint32_t cg = __popc(col);
+          const uint32_t inc = warp_incl_scan(cg, lane);
+          band_stage_group(col, ids, lane, stage, inc - cg);
+          stage_delta[lane] = goff + k - (inc - cg);   // k = instances of this tile already written
+          band_flush(stage, stage_delta, __shfl_sync(0xffffffffu, inc, 31), lane, out);
+          k += cg;
+        }
+        __syncwarp();
       }
     }
     if (!WRITE) {
@@ -340,10 +358,9 @@ __global__ void __launch_bounds__(256) band_tile_scan_kernel(int nL, int NB, int
   }
 }
 
-inline cudaError_t band_bin(const BandWs& w, int P, int gx, int gy, int64_t R, const uint32_t* sorted_idx,
+inline cudaError_t band_bin(const BandWs& w, int P, const uint32_t* nvalid, int gx, int gy, int64_t R, const uint32_t* sorted_idx,
                             const uint2* srect, const uint2* rect, uint32_t* out, uint2* ranges, cudaStream_t st) {
   const int NB = band_count(gx), nL = NB * gy, nchunks = band_row_chunks(nL), T = gx * gy;
-  const int per_warp = ((P + nchunks - 1) / nchunks + 31) & ~31;
   const size_t smA = (size_t)kBandWarps * (nL + gy + NB) * sizeof(uint32_t);
   const int sb_words = (nL + 1 + 31) & ~31;
   const size_t smC = (size_t)sb_words * sizeof(uint32_t);
@@ -371,7 +388,7 @@ inline cudaError_t band_bin(const BandWs& w, int P, int gx, int gy, int64_t R, c
   // one timed phase per kernel (opt-in phase timer): bench.py reports the roofline of a single kernel
   {
     Phase ph("band_rows_kernel<count>", st);
-    band_rows_kernel<false><<<ctasA, kBandWarps * 32, smA, st>>>(P, per_warp, NB, gy, nchunks, sorted_idx, srect, w.matA,
+    band_rows_kernel<false><<<ctasA, kBandWarps * 32, smA, st>>>(P, nvalid, NB, gy, nchunks, sorted_idx, srect, w.matA,
                                                                  nullptr, nullptr);
   }
   {
@@ -380,7 +397,7 @@ inline cudaError_t band_bin(const BandWs& w, int P, int gx, int gy, int64_t R, c
   }
   {
     Phase ph("band_rows_kernel<write>", st);
-    band_rows_kernel<true><<<ctasA, kBandWarps * 32, smA, st>>>(P, per_warp, NB, gy, nchunks, sorted_idx, srect, w.matA,
+    band_rows_kernel<true><<<ctasA, kBandWarps * 32, smA, st>>>(P, nvalid, NB, gy, nchunks, sorted_idx, srect, w.matA,
                                                                 w.lstart, w.recs);
   }
   {

@@ -40,6 +40,7 @@ struct GeomWs {
   uint32_t* tiles;        // [P] tiles touched
   uint32_t* wts;          // [P] binning cost weight of the Gaussian (bin_weight(tiles))
   uint32_t* wtotal;       // [1] sum of wts (device scalar written by the scan)
+  uint32_t* nvalid;       // [1] number of depth-sorted Gaussians: the visible ones on the band path (culled dropped), else P
   uint2* rect;            // [P] x0 | x1<<16 , y0 | y1<<16 (0,0 when culled)
   uint2* srect;           // [P] rect in depth order (rect[sorted_idx[i]])
   uint32_t* keyA;         // [P] sort ping
@@ -66,6 +67,7 @@ inline size_t carve_geom(int variant, int P, void* base, GeomWs* ws) {
   w.tiles = c.take<uint32_t>(p);
   w.wts = c.take<uint32_t>(p);
   w.wtotal = c.take<uint32_t>(4);
+  w.nvalid = w.wtotal ? w.wtotal + 1 : nullptr;
   w.rect = c.take<uint2>(p);
   w.srect = c.take<uint2>(p);
   w.keyA = c.take<uint32_t>(p);
@@ -389,9 +391,11 @@ __global__ void __launch_bounds__(256) bin_ranges_kernel(int num_tiles, int nchu
 }
 
 __global__ void __launch_bounds__(256) gather_rect_kernel(int P, const uint32_t* __restrict__ sorted_idx,
-                                                          const uint2* __restrict__ rect, uint2* __restrict__ srect) {
+                                                          const uint2* __restrict__ rect, uint2* __restrict__ srect,
+                                                          const uint32_t* __restrict__ n_dev = nullptr) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < P) srect[i] = rect[sorted_idx[i]];
+  const int n = n_dev ? min(P, (int)*n_dev) : P;
+  if (i < n) srect[i] = rect[sorted_idx[i]];
 }
 
 // Depth argsort + offsets (stage 1 tail).  Leaves Gaussian ids in ws.sorted_idx.
@@ -401,25 +405,30 @@ inline cudaError_t depth_order_and_offsets(const GeomWs& ws, int P, bool fast, c
   cudaError_t e;
   const uint32_t n = (uint32_t)P;
   const uint32_t nblk = sort_num_blocks(n);
+  const bool compact = !need_offsets;   // band path: only the visible Gaussians are sorted (count in ws.nvalid)
   if (depth_sort_coop_fits(nblk)) {
     DepthSortArgs a;
     a.dkey = ws.dkey; a.keyA = ws.keyA; a.valA = ws.valA; a.keyB = ws.keyB; a.valB = ws.sorted_idx;
-    a.hist = ws.sort_scratch; a.bsum = ws.sort_scratch + (size_t)2 * nblk * 256; a.dtot = a.bsum + nblk;
+    a.hist = ws.sort_scratch; a.accum = ws.sort_scratch + (size_t)2 * nblk * 256; a.bsum = a.accum + 4 * kSortAccumWords;
     a.wsrc = need_offsets ? (fast ? ws.wts : ws.tiles) : nullptr; a.rect = ws.rect; a.srect = ws.srect; a.offsets = ws.offsets;
     a.total_out = fast ? ws.wtotal : nullptr;
-    a.n = n; a.nblk = nblk;
+    a.nvalid = ws.nvalid;
+    a.n = n; a.nblk = nblk; a.compact = compact ? 1 : 0;
     return depth_sort_coop(a, st);
   }
-  // 4 stable passes, 8 bits each: (dkey,iota)->(A,valA)->(B,sorted)->(A,valA)->(-,sorted)
-  e = radix_pass<uint32_t, true, true>(ws.dkey, nullptr, ws.keyA, ws.valA, n, 0, 8, ws.sort_scratch, st);
+  // 4 stable passes, 8 bits each: (dkey,iota)->(A,valA)->(B,sorted)->(A,valA)->(-,sorted); in compact mode the
+  // first pass drops the culled keys and the later ones run on the device-side count
+  const uint32_t* nd = compact ? ws.nvalid : nullptr;
+  if (compact) e = radix_pass<uint32_t, true, true, true>(ws.dkey, nullptr, ws.keyA, ws.valA, n, 0, 8, ws.sort_scratch, st, nullptr, ws.nvalid);
+  else e = radix_pass<uint32_t, true, true>(ws.dkey, nullptr, ws.keyA, ws.valA, n, 0, 8, ws.sort_scratch, st);
   if (e != cudaSuccess) return e;
-  e = radix_pass<uint32_t, false, true>(ws.keyA, ws.valA, ws.keyB, ws.sorted_idx, n, 8, 8, ws.sort_scratch, st);
+  e = radix_pass<uint32_t, false, true>(ws.keyA, ws.valA, ws.keyB, ws.sorted_idx, n, 8, 8, ws.sort_scratch, st, nd);
   if (e != cudaSuccess) return e;
-  e = radix_pass<uint32_t, false, true>(ws.keyB, ws.sorted_idx, ws.keyA, ws.valA, n, 16, 8, ws.sort_scratch, st);
+  e = radix_pass<uint32_t, false, true>(ws.keyB, ws.sorted_idx, ws.keyA, ws.valA, n, 16, 8, ws.sort_scratch, st, nd);
   if (e != cudaSuccess) return e;
-  e = radix_pass<uint32_t, false, false>(ws.keyA, ws.valA, ws.keyB, ws.sorted_idx, n, 24, 8, ws.sort_scratch, st);
+  e = radix_pass<uint32_t, false, false>(ws.keyA, ws.valA, ws.keyB, ws.sorted_idx, n, 24, 8, ws.sort_scratch, st, nd);
   if (e != cudaSuccess) return e;
-  gather_rect_kernel<<<div_up(P, 256), 256, 0, st>>>(P, ws.sorted_idx, ws.rect, ws.srect);
+  gather_rect_kernel<<<div_up(P, 256), 256, 0, st>>>(P, ws.sorted_idx, ws.rect, ws.srect, nd);
   if (!need_offsets) return cudaGetLastError();
   if (fast) return exclusive_scan_u32(ws.wts, ws.sorted_idx, n, ws.offsets, ws.sort_scratch, ws.wtotal, st);
   return exclusive_scan_u32(ws.tiles, ws.sorted_idx, n, ws.offsets, ws.sort_scratch, nullptr, st);
@@ -434,7 +443,7 @@ inline cudaError_t bin_instances(const GeomWs& g, const BinWs& b, const ImageWs&
   if (e != cudaSuccess) return e;
   *point_list = b.valA;
   if (R <= 0 || P <= 0) return cudaSuccess;
-  if (band_path(gx, gy)) return band_bin(b.band, P, gx, gy, R, g.sorted_idx, g.srect, g.rect, b.valA, im.ranges, st);
+  if (band_path(gx, gy)) return band_bin(b.band, P, g.nvalid, gx, gy, R, g.sorted_idx, g.srect, g.rect, b.valA, im.ranges, st);
   if (bin_fast_path(T)) {
     const int nchunks = bin_max_chunks(T);
     const int wpc = bin_warps_per_cta(T);

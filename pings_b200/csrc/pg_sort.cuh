@@ -175,12 +175,15 @@ constexpr int kSortChunk = kSortThreads * kSortIpt;  // 4096
 constexpr int kSortWarpItems = 32 * kSortIpt;         // 512
 
 // hist[d * nblk + blk] = number of items of block `blk` with digit d.
-template <typename KeyT>
+// n_dev (optional): device-side item count (<= n, the launch bound).  DROP: keys equal to all-ones are skipped
+// (compacting first pass of the depth sort: culled Gaussians).
+template <typename KeyT, bool DROP = false>
 __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(
     const KeyT* __restrict__ keys, uint32_t n, int shift, uint32_t nbins,
-    uint32_t* __restrict__ hist, uint32_t nblk) {
+    uint32_t* __restrict__ hist, uint32_t nblk, const uint32_t* __restrict__ n_dev = nullptr) {
   __shared__ uint32_t h[256];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (n_dev) n = min(n, *n_dev);
   h[threadIdx.x] = 0;
   __syncthreads();
   const uint32_t base = blockIdx.x * kSortChunk + warp * kSortWarpItems;
@@ -189,7 +192,11 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(
 #pragma unroll
   for (int it = 0; it < kSortIpt; ++it) {
     uint32_t i = base + it * 32 + lane;
-    d[it] = i < n ? ((uint32_t)(keys[i] >> shift) & mask) : 0xffffffffu;
+    d[it] = 0xffffffffu;
+    if (i < n) {
+      const KeyT kk = keys[i];
+      if (!(DROP && kk == (KeyT)~(KeyT)0)) d[it] = (uint32_t)(kk >> shift) & mask;
+    }
   }
 #pragma unroll
   for (int it = 0; it < kSortIpt; ++it) {
@@ -202,13 +209,17 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(
 
 // Stable scatter. `offs` is the exclusive scan of the digit-major histogram matrix.
 // IOTA: values are generated as the item index (first pass of an argsort).
-template <typename KeyT, bool IOTA, bool WRITE_KEYS>
+template <typename KeyT, bool IOTA, bool WRITE_KEYS, bool DROP = false>
 __global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(
     const KeyT* __restrict__ kin, const uint32_t* __restrict__ vin, KeyT* __restrict__ kout,
     uint32_t* __restrict__ vout, uint32_t n, int shift, uint32_t nbins,
-    const uint32_t* __restrict__ offs, uint32_t nblk) {
+    const uint32_t* __restrict__ offs, uint32_t nblk, const uint32_t* __restrict__ n_dev = nullptr) {
   __shared__ uint32_t wh[kSortWarps][256];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (n_dev) {
+    n = min(n, *n_dev);
+    if (blockIdx.x * kSortChunk >= n) return;   // uniform per block
+  }
 #pragma unroll
   for (int w = 0; w < kSortWarps; ++w) wh[w][threadIdx.x] = 0;
   __syncthreads();
@@ -231,7 +242,7 @@ __global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(
 #pragma unroll
   for (int it = 0; it < kSortIpt; ++it) {
     uint32_t i = base + it * 32 + lane;
-    uint32_t d = i < n ? ((uint32_t)(k[it] >> shift) & mask) : 0xffffffffu;
+    uint32_t d = (i < n && !(DROP && k[it] == (KeyT)~(KeyT)0)) ? ((uint32_t)(k[it] >> shift) & mask) : 0xffffffffu;
     uint32_t peers = __match_any_sync(0xffffffffu, d);
     if (d != 0xffffffffu && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
     __syncwarp();
@@ -252,7 +263,7 @@ __global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(
 #pragma unroll
   for (int it = 0; it < kSortIpt; ++it) {
     uint32_t i = base + it * 32 + lane;
-    bool valid = i < n;
+    bool valid = i < n && !(DROP && k[it] == (KeyT)~(KeyT)0);
     uint32_t d = valid ? ((uint32_t)(k[it] >> shift) & mask) : 0xffffffffu;
     uint32_t peers = __match_any_sync(0xffffffffu, d);
     uint32_t pos = 0;
@@ -275,19 +286,25 @@ inline size_t sort_scratch_elems(uint64_t n) {
 }
 
 // One stable pass on bits [shift, shift+bits) (bits <= 8).
-template <typename KeyT, bool IOTA, bool WRITE_KEYS>
+// n_dev: optional device-side item count (the grids are sized for n).  DROP: skip all-ones keys; the number of
+// kept items is then written to *kept_out (device) by the histogram scan.
+template <typename KeyT, bool IOTA, bool WRITE_KEYS, bool DROP = false>
 inline cudaError_t radix_pass(const KeyT* kin, const uint32_t* vin, KeyT* kout, uint32_t* vout,
-                              uint32_t n, int shift, int bits, uint32_t* scratch, cudaStream_t st) {
-  if (n == 0) return cudaSuccess;
+                              uint32_t n, int shift, int bits, uint32_t* scratch, cudaStream_t st,
+                              const uint32_t* n_dev = nullptr, uint32_t* kept_out = nullptr) {
+  if (n == 0) {
+    if (kept_out) return cudaMemsetAsync(kept_out, 0, sizeof(uint32_t), st);
+    return cudaSuccess;
+  }
   const uint32_t nblk = sort_num_blocks(n);
   const uint32_t nbins = 1u << bits;
   uint32_t* hist = scratch;
   uint32_t* scan_scratch = scratch + (size_t)nblk * 256;
-  radix_hist_kernel<KeyT><<<nblk, kSortThreads, 0, st>>>(kin, n, shift, nbins, hist, nblk);
-  cudaError_t e = exclusive_scan_u32(hist, nullptr, nbins * nblk, hist, scan_scratch, nullptr, st);
+  radix_hist_kernel<KeyT, DROP><<<nblk, kSortThreads, 0, st>>>(kin, n, shift, nbins, hist, nblk, n_dev);
+  cudaError_t e = exclusive_scan_u32(hist, nullptr, nbins * nblk, hist, scan_scratch, kept_out, st);
   if (e != cudaSuccess) return e;
-  radix_scatter_kernel<KeyT, IOTA, WRITE_KEYS><<<nblk, kSortThreads, 0, st>>>(
-      kin, vin, kout, vout, n, shift, nbins, hist, nblk);
+  radix_scatter_kernel<KeyT, IOTA, WRITE_KEYS, DROP><<<nblk, kSortThreads, 0, st>>>(
+      kin, vin, kout, vout, n, shift, nbins, hist, nblk, n_dev);
   return cudaGetLastError();
 }
 
@@ -296,11 +313,19 @@ inline cudaError_t radix_pass(const KeyT* kin, const uint32_t* vin, KeyT* kout, 
 // when run pass by pass).  For P <= kCoopSortMaxBlocks * 4096 the four LSD passes, the depth-order
 // gather of the tile rects and the exclusive scan of the binning weights run as ONE cooperative
 // kernel: a CTA keeps its 4096 (key, value) pairs in registers between the counting and the scatter
-// half of a pass; the [block][digit] histogram matrix stays in L2, one warp per digit turns its column
-// into exclusive prefixes over the blocks (ten independent loads per lane) and each CTA then reads
-// just its own row plus the 256 digit totals, so a pass costs three grid barriers and no scan kernels.
-// (Letting every CTA sum all rows itself saves a barrier but costs 12 us per pass in serial L2 latency.)
-constexpr uint32_t kCoopSortMaxBlocks = 296;  // 2 CTAs per SM; above this every CTA re-reading the matrix dominates
+// half of a pass.  Cross-CTA digit prefixes without a scan phase: every CTA stores its 256 digit counts as
+// a row of the [block][digit] matrix and adds them (RED.ADD) into the row of its group of 8 CTAs and into
+// the digit totals; after ONE grid barrier a CTA sums the rows of the groups before its own (<= 36) and of
+// the CTAs before it inside its group (<= 7) - 2 grid barriers per pass instead of 3 (13 -> 8 in total).
+//
+// COMPACT mode (band binning): culled Gaussians (key 0xFFFFFFFF) are dropped in pass 0, so passes 1-3, the
+// rect gather and everything downstream work on the V valid Gaussians only (V stays on the device, *nvalid):
+// 5 M-Gaussian maps have V ~ 1 M per view.
+constexpr uint32_t kCoopSortMaxBlocks = 296;  // 2 CTAs per SM
+constexpr uint32_t kSortGroup = 8;            // CTAs per group row
+constexpr uint32_t kSortMaxGroups = (kCoopSortMaxBlocks + kSortGroup - 1) / kSortGroup;   // 37
+// u32 words of accumulation scratch per pass: group rows + digit totals; zeroed by the host before the launch
+constexpr size_t kSortAccumWords = (size_t)(kSortMaxGroups + 1) * 256;
 
 struct DepthSortArgs {
   const uint32_t* dkey;   // [n] keys (read only)
@@ -308,21 +333,23 @@ struct DepthSortArgs {
   uint32_t* valA;
   uint32_t* keyB;         // pong (keys of the last pass are never written)
   uint32_t* valB;         // final argsort
-  uint32_t* hist;         // [2][nblk][256] double-buffered histogram matrix
+  uint32_t* hist;         // [2][nblk][256] double-buffered row matrix
+  uint32_t* accum;        // [4][kSortAccumWords] zero-initialised group rows + totals, one set per pass
   uint32_t* bsum;         // [nblk] tail scan block sums
-  uint32_t* dtot;         // [2][256] digit totals of the current pass
   const uint32_t* wsrc;   // [n] per-item weight, gathered through the argsort (NULL: skip the scan)
   const uint2* rect;      // [n] per-item rect, gathered through the argsort
   uint2* srect;           // [n] out
   uint32_t* offsets;      // [n] out: exclusive scan of wsrc in sorted order
   uint32_t* total_out;    // nullable: grand total of wsrc
+  uint32_t* nvalid;       // out: number of sorted items (n, or the number of valid keys in compact mode)
   uint32_t n, nblk;
+  int compact;            // drop keys == 0xFFFFFFFF in pass 0
 };
 
 inline size_t depth_sort_scratch_elems(uint64_t n) {
   const size_t nblk = sort_num_blocks(n);
-  const size_t coop = 2 * nblk * 256 + nblk + 512 + 64;
-  const size_t plain = sort_scratch_elems(n);
+  const size_t coop = 2 * nblk * 256 + 4 * kSortAccumWords + nblk + 64;
+  const size_t plain = sort_scratch_elems(n) + 64;
   return coop > plain ? coop : plain;
 }
 
@@ -331,9 +358,11 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
   cg::grid_group grid = cg::this_grid();
   __shared__ uint32_t wh[kSortWarps][256];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t blk = blockIdx.x, n = a.n, nblk = a.nblk;
+  const uint32_t blk = blockIdx.x, nblk = a.nblk;
   const uint32_t base = blk * kSortChunk + warp * kSortWarpItems;
   const uint32_t lt = (1u << lane) - 1u;
+  const uint32_t grp = blk / kSortGroup;
+  uint32_t n = a.n;   // items of the current pass (pass 0: all; later: the valid ones in compact mode)
 #pragma unroll 1
   for (int pass = 0; pass < 4; ++pass) {
     const int shift = pass * 8;
@@ -342,23 +371,29 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
     uint32_t* kout = (pass & 1) ? a.keyB : a.keyA;
     uint32_t* vout = (pass & 1) ? a.valB : a.valA;
     uint32_t* hist = a.hist + (size_t)(pass & 1) * nblk * 256;
+    uint32_t* gsum = a.accum + (size_t)pass * kSortAccumWords;         // [groups][256]
+    uint32_t* dtot = gsum + (size_t)kSortMaxGroups * 256;               // [256]
 #pragma unroll
     for (int w = 0; w < kSortWarps; ++w) wh[w][threadIdx.x] = 0;
     __syncthreads();
     uint32_t k[kSortIpt], v[kSortIpt];
+    const bool drop = a.compact && pass == 0;
 #pragma unroll
     for (int it = 0; it < kSortIpt; ++it) {
       const uint32_t i = base + it * 32 + lane;
       // .cg: pass >= 1 reads what other CTAs wrote earlier in this launch
-      k[it] = i < n ? __ldcg(kin + i) : 0u;
+      k[it] = i < n ? __ldcg(kin + i) : 0xffffffffu;
       v[it] = i < n ? (pass == 0 ? i : __ldcg(vin + i)) : 0u;
     }
+    uint32_t valid = 0;   // bit `it`: item takes part in this pass
 #pragma unroll
     for (int it = 0; it < kSortIpt; ++it) {
       const uint32_t i = base + it * 32 + lane;
-      const uint32_t d = i < n ? ((k[it] >> shift) & 255u) : 0xffffffffu;
+      const bool ok = i < n && !(drop && k[it] == 0xffffffffu);
+      valid |= ok ? (1u << it) : 0u;
+      const uint32_t d = ok ? ((k[it] >> shift) & 255u) : 0xffffffffu;
       const uint32_t peers = __match_any_sync(0xffffffffu, d);
-      if (d != 0xffffffffu && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
+      if (ok && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
       __syncwarp();
     }
     __syncthreads();
@@ -367,37 +402,25 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
 #pragma unroll
       for (int w = 0; w < kSortWarps; ++w) c += wh[w][threadIdx.x];
       hist[(size_t)blk * 256 + threadIdx.x] = c;
-    }
-    grid.sync();
-    // column scans: a warp owns digit gw (striding when the grid has fewer than 256 warps) and turns its column of the matrix into exclusive
-    // prefixes over the blocks (in place) plus the digit total - 10 independent loads per lane instead
-    // of every CTA walking all rows
-    {
-      for (uint32_t gw = blk * kSortWarps + warp; gw < 256u; gw += nblk * kSortWarps) {
-        uint32_t v[kCoopSortMaxBlocks / 32 + 1];
-#pragma unroll
-        for (int q = 0; q < (int)(kCoopSortMaxBlocks / 32 + 1); ++q) {
-          const uint32_t b = q * 32 + lane;
-          v[q] = b < nblk ? __ldcg(hist + (size_t)b * 256 + gw) : 0u;
-        }
-        uint32_t carry = 0;
-#pragma unroll
-        for (int q = 0; q < (int)(kCoopSortMaxBlocks / 32 + 1); ++q) {
-          const uint32_t b = q * 32 + lane;
-          const uint32_t inc = warp_incl_scan(v[q], lane);
-          if (b < nblk) hist[(size_t)b * 256 + gw] = carry + inc - v[q];
-          carry += __shfl_sync(0xffffffffu, inc, 31);
-        }
-        if (lane == 0) a.dtot[(pass & 1) * 256 + gw] = carry;
+      if (c) {
+        atomicAdd(gsum + (size_t)grp * 256 + threadIdx.x, c);
+        atomicAdd(dtot + threadIdx.x, c);
       }
     }
     grid.sync();
     {
-      // digit = threadIdx.x: items of this digit in earlier blocks, and in all blocks
-      const uint32_t below = __ldcg(hist + (size_t)blk * 256 + threadIdx.x);
-      const uint32_t all = __ldcg(a.dtot + (pass & 1) * 256 + threadIdx.x);
+      // digit = threadIdx.x: items of this digit in earlier blocks (group rows before mine + rows of the CTAs
+      // before me in my group), and in all blocks
+      uint32_t below = 0;
+      for (uint32_t g = 0; g < grp; ++g) below += __ldcg(gsum + (size_t)g * 256 + threadIdx.x);
+      for (uint32_t b = grp * kSortGroup; b < blk; ++b) below += __ldcg(hist + (size_t)b * 256 + threadIdx.x);
+      const uint32_t all = __ldcg(dtot + threadIdx.x);
       uint32_t tot;
       uint32_t run = block_excl_scan_256(all, &tot) + below;
+      if (pass == 0) {
+        n = tot;   // number of valid items (== a.n unless compact)
+        if (blk == 0 && threadIdx.x == 0 && a.nvalid) *a.nvalid = tot;
+      }
 #pragma unroll
       for (int w = 0; w < kSortWarps; ++w) {
         const uint32_t c = wh[w][threadIdx.x];
@@ -408,17 +431,16 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
     __syncthreads();
 #pragma unroll
     for (int it = 0; it < kSortIpt; ++it) {
-      const uint32_t i = base + it * 32 + lane;
-      const bool valid = i < n;
-      const uint32_t d = valid ? ((k[it] >> shift) & 255u) : 0xffffffffu;
+      const bool ok = (valid >> it) & 1u;
+      const uint32_t d = ok ? ((k[it] >> shift) & 255u) : 0xffffffffu;
       const uint32_t peers = __match_any_sync(0xffffffffu, d);
-      if (valid) {
+      if (ok) {
         const uint32_t pos = wh[warp][d] + __popc(peers & lt);
         if (pass < 3) kout[pos] = k[it];
         vout[pos] = v[it];
       }
       __syncwarp();
-      if (valid && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
+      if (ok && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
       __syncwarp();
     }
     grid.sync();
@@ -478,6 +500,8 @@ inline bool depth_sort_coop_fits(uint32_t nblk) {
 }
 
 inline cudaError_t depth_sort_coop(DepthSortArgs a, cudaStream_t st) {
+  cudaError_t e = cudaMemsetAsync(a.accum, 0, 4 * kSortAccumWords * sizeof(uint32_t), st);
+  if (e != cudaSuccess) return e;
   void* params[] = {(void*)&a};
   return cudaLaunchCooperativeKernel((const void*)depth_sort_coop_kernel, dim3(a.nblk), dim3(kSortThreads), params, 0, st);
 }
