@@ -273,6 +273,64 @@ int pg_sdf_query(const PgNeuralMap* map, const PgQueryArgs* args, const PgMlp* m
                  const float* query_xyz, float* sdf, float* sdf_std, int64_t* nn_counts, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * spawn_gaussians epilogue (gaussian_splatting/gaussian_renderer/__init__.py:551-764 with the quaternion helpers of
+ * utils/tools.py:743-751,811-844): what the reference runs as ~60 eager torch kernels between the five decoder
+ * heads and the rasterizer.  Raw head outputs are [n, out*K] row-major (Gaussian r = i*K + k reads `out` floats at
+ * out*r, the reference's .view(NK, -1)).
+ * ---------------------------------------------------------------------------------------- */
+typedef struct PgSpawnArgs {
+  int64_t n;                 /* spawning neural points */
+  int32_t K;                 /* Gaussians per point (Decoder.out_k) */
+  const int64_t* sidx;       /* [n] row of each spawning point in the point arrays, or NULL (identity) */
+  const float* position;     /* [N,3] */
+  const float* orientation;  /* [N,4] (w,x,y,z) */
+  const float* color;        /* [N,3] or NULL */
+  const float* cam_origin;   /* [3] or NULL */
+  const float *xyz_raw, *rot_raw, *scale_raw, *alpha_raw, *color_raw;   /* [n,3K] [n,4K] [n,3K] [n,K] [n,3K] */
+  float disp_range;          /* displacement_range_ratio * resolution (GR:605) */
+  float unit_scale;          /* unit_scale_ratio * resolution (GR:661) */
+  float max_scale;           /* max_scale_ratio * resolution (GR:654) */
+  float z_far;               /* > 0: dist_adaptive_scale (GR:656-659), else off */
+  float scale_filter;        /* >= 0: scale_filter_on with this threshold (GR:739-751), else off */
+  int32_t surfel;            /* third scale = 1e-7 (GR:667-670) */
+  int32_t residual;          /* clamp(base + 0.1 tanh(.), 0, 1) (GR:706-711) else sigmoid(.) */
+  int32_t alpha_filter;      /* keep alpha > 0 only (GR:727-737) */
+  int32_t xy_only;           /* view_direction_xy_only (GR:592) */
+} PgSpawnArgs;
+
+typedef struct PgSpawnOut {
+  float *xyz, *scale, *rot, *alpha, *color;   /* compacted, capacity n*K rows: [.,3] [.,3] [.,4] [.,1] [.,3] */
+  float* alpha_all;                           /* dense [n*K] (GR:717) */
+  int32_t* cpos;                              /* dense [n*K]: compact row of the Gaussian, -1 when dropped */
+  uint8_t* free_out;                          /* compacted gaussian_free_mask or NULL */
+  const uint8_t* free_mask;                   /* [N] per point or NULL */
+  uint32_t* state;                            /* [pg_spawn_state_words(n*K)] scratch; after the call state[blocks+1] =
+                                                 number of kept Gaussians, state[blocks+2] = 1 if a rotation is NaN */
+} PgSpawnOut;
+
+typedef struct PgSpawnGrads {
+  const float *d_xyz, *d_scale, *d_rot, *d_alpha, *d_color;   /* compacted cotangents, any may be NULL */
+  const float* d_alpha_all;                                   /* dense [n*K] or NULL */
+  const int32_t* cpos;                                        /* from the forward */
+  float *d_xyz_raw, *d_rot_raw, *d_scale_raw, *d_alpha_raw, *d_color_raw;   /* dense, fully written */
+} PgSpawnGrads;
+
+/* Gather the feature rows of the spawning points into the decoder inputs: geo_in [n, Fg (+1 view distance if
+ * dist_concat)], color_in [n, Fc (+3 view direction in the point frame if view_concat)] (GR:563-569,587-597,677-698);
+ * color_in may be NULL. */
+int pg_spawn_prepare(int64_t n, const int64_t* sidx, const float* position, const float* orientation,
+                     const float* cam_origin, const float* geo_feature, int Fg, const float* color_feature, int Fc,
+                     int dist_concat, int view_concat, int xy_only, float* geo_in, float* color_in, void* stream);
+/* d_feature[sidx[i], :F] += d_in[i, :F] (adjoint of the gather; d_in rows are in_w wide). */
+int pg_spawn_prepare_backward(int64_t n, const int64_t* sidx, const float* d_in, int in_w, int F, float* d_feature,
+                              void* stream);
+size_t pg_spawn_state_words(int64_t NK);
+/* Word index of the kept-Gaussian count inside `state` (the NaN flag follows it). */
+size_t pg_spawn_count_index(int64_t NK);
+int pg_spawn_epilogue_forward(const PgSpawnArgs* args, const PgSpawnOut* out, void* stream);
+int pg_spawn_epilogue_backward(const PgSpawnArgs* args, const PgSpawnGrads* grads, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Post-raster loss assembly (utils/mapper.py:1239,1252-1267): loss = mean|rgb - gt_rgb| +
  * lambda_depth * mean over valid pixels of |gt_depth - depth| (or |1/gt_depth - 1/depth| when
  * inverse_depth), valid = depth_min < gt_depth < depth_max [and alpha > min_alpha].  depth/gt_depth
@@ -287,6 +345,21 @@ int pg_photo_depth_loss_forward(int H, int W, const float* rgb, const float* gt_
 int pg_photo_depth_loss_backward(int H, int W, float lambda_depth, const float* upstream, const double* sums,
                                  const float* seed_rgb, const float* seed_depth, float* d_rgb, float* d_depth,
                                  void* stream);
+
+/* depth2normal (gaussian_splatting/utils/point_utils.py:83-148): camera-frame normal map [3,H,W] from a depth map
+ * [H,W] and the visibility mask (alpha > min_alpha); cx, cy, fx, fy are in pixels of the (down-scaled) image
+ * (prcppoint * size / img_scale, f / img_scale).  alpha (optional) multiplies the output, as GR:381-382 does with
+ * the detached rendered alpha.  The backward overwrites d_depth [H,W]. */
+int pg_depth2normal_forward(int H, int W, float cx, float cy, float fx, float fy, const float* depth, const uint8_t* mask,
+                            const float* alpha, float* normal, void* stream);
+int pg_depth2normal_backward(int H, int W, float cx, float cy, float fx, float fy, const float* depth, const uint8_t* mask,
+                             const float* alpha, const float* d_normal, float* d_depth, void* stream);
+/* Affine exposure correction (GR:449-458): out[3,H,W] = mat[3,3] * rgb + offset[3] per pixel.  The backward
+ * overwrites d_img (may be NULL) and d_mat_off[12] = (d_mat row-major, d_offset). */
+int pg_exposure_affine_forward(int H, int W, const float* img, const float* mat, const float* offset, float* out,
+                               void* stream);
+int pg_exposure_affine_backward(int H, int W, const float* img, const float* mat, const float* d_out, float* d_img,
+                                float* d_mat_off, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Fused SSIM (FS/ssim.h:7-26: fusedssim, fusedssim_backward).  img*: [B,C,H,W] contiguous fp32.

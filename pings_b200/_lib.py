@@ -79,6 +79,25 @@ class PgMlp(C.Structure):
                 ("leaky_relu", C.c_int32), ("weights", fp * PG_MLP_MAX_LAYERS), ("biases", fp * PG_MLP_MAX_LAYERS)]
 
 
+class PgSpawnArgs(C.Structure):
+    _fields_ = [("n", C.c_int64), ("K", C.c_int32), ("sidx", fp), ("position", fp), ("orientation", fp), ("color", fp),
+                ("cam_origin", fp), ("xyz_raw", fp), ("rot_raw", fp), ("scale_raw", fp), ("alpha_raw", fp),
+                ("color_raw", fp), ("disp_range", C.c_float), ("unit_scale", C.c_float), ("max_scale", C.c_float),
+                ("z_far", C.c_float), ("scale_filter", C.c_float), ("surfel", C.c_int32), ("residual", C.c_int32),
+                ("alpha_filter", C.c_int32), ("xy_only", C.c_int32)]
+
+
+class PgSpawnOut(C.Structure):
+    _fields_ = [("xyz", fp), ("scale", fp), ("rot", fp), ("alpha", fp), ("color", fp), ("alpha_all", fp), ("cpos", fp),
+                ("free_out", fp), ("free_mask", fp), ("state", fp)]
+
+
+class PgSpawnGrads(C.Structure):
+    _fields_ = [("d_xyz", fp), ("d_scale", fp), ("d_rot", fp), ("d_alpha", fp), ("d_color", fp), ("d_alpha_all", fp),
+                ("cpos", fp), ("d_xyz_raw", fp), ("d_rot_raw", fp), ("d_scale_raw", fp), ("d_alpha_raw", fp),
+                ("d_color_raw", fp)]
+
+
 class PingsB200LibraryMissing(ImportError):
     pass
 
@@ -151,6 +170,26 @@ def lib() -> C.CDLL:
     L.pg_ssim_forward.argtypes = [C.c_int] * 4 + [C.c_float] * 2 + [fp] * 7
     L.pg_ssim_backward.restype = C.c_int
     L.pg_ssim_backward.argtypes = [C.c_int] * 4 + [C.c_float] * 2 + [fp, fp, fp, C.c_float, fp, fp, fp, fp, fp]
+    L.pg_depth2normal_forward.restype = C.c_int
+    L.pg_depth2normal_forward.argtypes = [C.c_int, C.c_int] + [C.c_float] * 4 + [fp] * 5
+    L.pg_depth2normal_backward.restype = C.c_int
+    L.pg_depth2normal_backward.argtypes = [C.c_int, C.c_int] + [C.c_float] * 4 + [fp] * 6
+    L.pg_exposure_affine_forward.restype = C.c_int
+    L.pg_exposure_affine_forward.argtypes = [C.c_int, C.c_int] + [fp] * 5
+    L.pg_exposure_affine_backward.restype = C.c_int
+    L.pg_exposure_affine_backward.argtypes = [C.c_int, C.c_int] + [fp] * 6
+    L.pg_spawn_prepare.restype = C.c_int
+    L.pg_spawn_prepare.argtypes = [C.c_int64, fp, fp, fp, fp, fp, C.c_int, fp, C.c_int, C.c_int, C.c_int, C.c_int, fp, fp, fp]
+    L.pg_spawn_prepare_backward.restype = C.c_int
+    L.pg_spawn_prepare_backward.argtypes = [C.c_int64, fp, fp, C.c_int, C.c_int, fp, fp]
+    L.pg_spawn_state_words.restype = C.c_size_t
+    L.pg_spawn_state_words.argtypes = [C.c_int64]
+    L.pg_spawn_count_index.restype = C.c_size_t
+    L.pg_spawn_count_index.argtypes = [C.c_int64]
+    L.pg_spawn_epilogue_forward.restype = C.c_int
+    L.pg_spawn_epilogue_forward.argtypes = [C.POINTER(PgSpawnArgs), C.POINTER(PgSpawnOut), fp]
+    L.pg_spawn_epilogue_backward.restype = C.c_int
+    L.pg_spawn_epilogue_backward.argtypes = [C.POINTER(PgSpawnArgs), C.POINTER(PgSpawnGrads), fp]
     _declare_optional(L)
     _lib = L
     return L

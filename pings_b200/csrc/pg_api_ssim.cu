@@ -72,4 +72,46 @@ int pg_photo_depth_loss_backward(int H, int W, float lambda_depth, const float* 
   return PG_OK;
 }
 
+int pg_depth2normal_forward(int H, int W, float cx, float cy, float fx, float fy, const float* depth, const uint8_t* mask,
+                            const float* alpha, float* normal, void* stream) {
+  if (H <= 0 || W <= 0 || !depth || !mask || !normal || fx == 0.f || fy == 0.f) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  D2NArgs a{H, W, cx, cy, 1.f / fx, 1.f / fy, depth, mask, alpha};
+  Phase ph("depth2normal_fwd", st);
+  depth2normal_fwd_kernel<<<div_up(H * W, 256), 256, 0, st>>>(a, normal);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_depth2normal_backward(int H, int W, float cx, float cy, float fx, float fy, const float* depth, const uint8_t* mask,
+                             const float* alpha, const float* d_normal, float* d_depth, void* stream) {
+  if (H <= 0 || W <= 0 || !depth || !mask || !d_normal || !d_depth || fx == 0.f || fy == 0.f) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  D2NArgs a{H, W, cx, cy, 1.f / fx, 1.f / fy, depth, mask, alpha};
+  PG_CUDA(cudaMemsetAsync(d_depth, 0, sizeof(float) * (size_t)H * W, st));
+  Phase ph("depth2normal_bwd", st);
+  depth2normal_bwd_kernel<<<div_up(H * W, 256), 256, 0, st>>>(a, d_normal, d_depth);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_exposure_affine_forward(int H, int W, const float* img, const float* mat, const float* offset, float* out,
+                               void* stream) {
+  if (H <= 0 || W <= 0 || !img || !mat || !offset || !out) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  exposure_fwd_kernel<<<min(div_up(H * W, 256), 148 * 8), 256, 0, st>>>(H * W, img, mat, offset, out);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_exposure_affine_backward(int H, int W, const float* img, const float* mat, const float* d_out, float* d_img,
+                                float* d_mat_off, void* stream) {
+  if (H <= 0 || W <= 0 || !img || !mat || !d_out || !d_mat_off) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  PG_CUDA(cudaMemsetAsync(d_mat_off, 0, 12 * sizeof(float), st));
+  exposure_bwd_kernel<<<min(div_up(H * W, 256), 148 * 4), 256, 0, st>>>(H * W, img, mat, d_out, d_img, d_mat_off);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
 }  // extern "C"

@@ -248,9 +248,18 @@ __global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(
     __syncwarp();
   }
   __syncthreads();
-  // digit = threadIdx.x: turn counts into starting offsets (global base + earlier warps)
-  if (threadIdx.x < nbins) {
-    uint32_t run = offs[threadIdx.x * nblk + blockIdx.x];
+  // digit = threadIdx.x: CTA-local start of the digit (exclusive scan of the CTA's digit counts) and the distance
+  // from a CTA-local slot to the global position (offs = global start of this CTA's items of the digit)
+  __shared__ KeyT sk[kSortChunk];
+  __shared__ uint32_t sv[kSortChunk];
+  __shared__ uint32_t gdelta[256];
+  uint32_t cta_items;
+  {
+    uint32_t mine = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) mine += wh[w][threadIdx.x];
+    uint32_t run = block_excl_scan_256(mine, &cta_items);
+    if (threadIdx.x < nbins) gdelta[threadIdx.x] = offs[threadIdx.x * nblk + blockIdx.x] - run;
 #pragma unroll
     for (int w = 0; w < kSortWarps; ++w) {
       uint32_t c = wh[w][threadIdx.x];
@@ -260,21 +269,32 @@ __global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(
   }
   __syncthreads();
   const uint32_t lt = (1u << lane) - 1u;
+  // exchange through shared memory so that the global stores go out in per-digit runs (see depth_sort_coop_kernel)
 #pragma unroll
   for (int it = 0; it < kSortIpt; ++it) {
     uint32_t i = base + it * 32 + lane;
     bool valid = i < n && !(DROP && k[it] == (KeyT)~(KeyT)0);
     uint32_t d = valid ? ((uint32_t)(k[it] >> shift) & mask) : 0xffffffffu;
     uint32_t peers = __match_any_sync(0xffffffffu, d);
-    uint32_t pos = 0;
     if (valid) {
-      pos = wh[warp][d] + __popc(peers & lt);
-      if (WRITE_KEYS) kout[pos] = k[it];
-      vout[pos] = v[it];
+      const uint32_t slot = wh[warp][d] + __popc(peers & lt);
+      sk[slot] = k[it];
+      sv[slot] = v[it];
     }
     __syncwarp();
     if (valid && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
     __syncwarp();
+  }
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < kSortIpt; ++q) {
+    const uint32_t slot = q * kSortThreads + threadIdx.x;
+    if (slot < cta_items) {
+      const KeyT key = sk[slot];
+      const uint32_t pos = slot + gdelta[(uint32_t)(key >> shift) & mask];
+      if (WRITE_KEYS) kout[pos] = key;
+      vout[pos] = sv[slot];
+    }
   }
 }
 
@@ -357,11 +377,14 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
   namespace cg = cooperative_groups;
   cg::grid_group grid = cg::this_grid();
   __shared__ uint32_t wh[kSortWarps][256];
+  __shared__ uint32_t sk[kSortChunk], sv[kSortChunk];   // exchange buffers (key, value) in CTA-local sorted order
+  __shared__ uint32_t gdelta[256];                      // digit -> global position minus CTA-local slot
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t blk = blockIdx.x, nblk = a.nblk;
   const uint32_t base = blk * kSortChunk + warp * kSortWarpItems;
   const uint32_t lt = (1u << lane) - 1u;
   const uint32_t grp = blk / kSortGroup;
+  uint32_t cta_items = 0;
   uint32_t n = a.n;   // items of the current pass (pass 0: all; later: the valid ones in compact mode)
 #pragma unroll 1
   for (int pass = 0; pass < 4; ++pass) {
@@ -411,16 +434,27 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
     {
       // digit = threadIdx.x: items of this digit in earlier blocks (group rows before mine + rows of the CTAs
       // before me in my group), and in all blocks
+      // (fully unrolled and predicated: up to 44 INDEPENDENT loads in flight; a counted loop serialises them on the
+      // L2 latency, ~0.7 us each)
       uint32_t below = 0;
-      for (uint32_t g = 0; g < grp; ++g) below += __ldcg(gsum + (size_t)g * 256 + threadIdx.x);
-      for (uint32_t b = grp * kSortGroup; b < blk; ++b) below += __ldcg(hist + (size_t)b * 256 + threadIdx.x);
+#pragma unroll
+      for (uint32_t g = 0; g < kSortMaxGroups; ++g)
+        if (g < grp) below += __ldcg(gsum + (size_t)g * 256 + threadIdx.x);
+#pragma unroll
+      for (uint32_t j = 0; j + 1 < kSortGroup; ++j)
+        if (grp * kSortGroup + j < blk) below += __ldcg(hist + (size_t)(grp * kSortGroup + j) * 256 + threadIdx.x);
       const uint32_t all = __ldcg(dtot + threadIdx.x);
       uint32_t tot;
-      uint32_t run = block_excl_scan_256(all, &tot) + below;
+      const uint32_t gstart = block_excl_scan_256(all, &tot) + below;   // global start of this CTA's items of the digit
       if (pass == 0) {
         n = tot;   // number of valid items (== a.n unless compact)
         if (blk == 0 && threadIdx.x == 0 && a.nvalid) *a.nvalid = tot;
       }
+      uint32_t mine = 0;
+#pragma unroll
+      for (int w = 0; w < kSortWarps; ++w) mine += wh[w][threadIdx.x];
+      uint32_t run = block_excl_scan_256(mine, &cta_items);             // CTA-local start of the digit
+      gdelta[threadIdx.x] = gstart - run;
 #pragma unroll
       for (int w = 0; w < kSortWarps; ++w) {
         const uint32_t c = wh[w][threadIdx.x];
@@ -429,19 +463,33 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
       }
     }
     __syncthreads();
+    // exchange through shared memory: items are placed at their CTA-local sorted slot first, so that the global
+    // stores below go out in runs of one digit (16 consecutive items on average) instead of 4-byte scatters -
+    // scattered 4-B stores cost a 32-B sector each and were the floor of the pass
 #pragma unroll
     for (int it = 0; it < kSortIpt; ++it) {
       const bool ok = (valid >> it) & 1u;
       const uint32_t d = ok ? ((k[it] >> shift) & 255u) : 0xffffffffu;
       const uint32_t peers = __match_any_sync(0xffffffffu, d);
       if (ok) {
-        const uint32_t pos = wh[warp][d] + __popc(peers & lt);
-        if (pass < 3) kout[pos] = k[it];
-        vout[pos] = v[it];
+        const uint32_t slot = wh[warp][d] + __popc(peers & lt);
+        sk[slot] = k[it];
+        sv[slot] = v[it];
       }
       __syncwarp();
       if (ok && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
       __syncwarp();
+    }
+    __syncthreads();
+#pragma unroll
+    for (int q = 0; q < kSortIpt; ++q) {
+      const uint32_t slot = q * kSortThreads + threadIdx.x;
+      if (slot < cta_items) {
+        const uint32_t key = sk[slot];
+        const uint32_t pos = slot + gdelta[(key >> shift) & 255u];
+        if (pass < 3) kout[pos] = key;
+        vout[pos] = sv[slot];
+      }
     }
     grid.sync();
   }

@@ -8,72 +8,135 @@ Differences from the reference, none of which changes results:
   extensions by their top-level names, GR:86-98); `gs_type == "2d_gs"` is not supported (that
   rasterizer is not vendored by the reference either, SURVEY.md §0.5);
 * the `get_time()` host synchronisations around every stage (GR:103,203) are dropped.
-The elementwise epilogue of `spawn_gaussians` is still eager torch (its fusion is the first "next"
-row of SURVEY.md §8f).
+The elementwise epilogue of `spawn_gaussians` runs as fused CUDA kernels
+(pings_b200/csrc/pg_spawn.cuh).
 """
 from __future__ import annotations
 
 import math
+import ctypes as C
 from typing import Dict, Optional
 
 import torch
 
-
-# ---- quaternion helpers (utils/tools.py:743-751, 811-844) --------------------------------------
-def apply_quaternion_rotation(quat: torch.Tensor, points: torch.Tensor) -> torch.Tensor:
-    """Passive rotation p' = q p q^-1 with q = (w, x, y, z)."""
-    quat_w = quat[..., 0].unsqueeze(-1)
-    quat_xyz = -quat[..., 1:]
-    t = 2 * torch.linalg.cross(quat_xyz, points)
-    return points + quat_w * t + torch.linalg.cross(quat_xyz, t)
-
-
-def quat_multiply(q1: torch.Tensor, q2: torch.Tensor) -> torch.Tensor:
-    w1, x1, y1, z1 = torch.unbind(q1, dim=1)
-    w2, x2, y2, z2 = torch.unbind(q2, dim=1)
-    w = w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2
-    x = w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2
-    y = w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2
-    z = w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2
-    return torch.stack((w, x, y, z), dim=1)
-
-
-def quat_inverse(quat: torch.Tensor) -> torch.Tensor:
-    w, x, y, z = torch.unbind(quat, dim=1)
-    return torch.stack((w, -x, -y, -z), dim=1)
-
-
-def depth2normal(depth, mask, camera, img_scale: int = 1):
-    """gaussian_splatting/utils/point_utils.py:83-148: normal map (camera frame, [3,H,W]) from a depth map."""
-    camD = depth.permute([1, 2, 0])
-    mask = mask.permute([1, 2, 0])
-    H, W, _ = camD.shape
-    device = camD.device
-    h, w = torch.meshgrid(torch.arange(H, device=device, dtype=torch.float32),
-                          torch.arange(W, device=device, dtype=torch.float32), indexing="ij")
-    p = torch.stack([w, h], dim=-1)
-    p[..., 0:1] -= camera.prcppoint[0] * camera.image_width / img_scale
-    p[..., 1:2] -= camera.prcppoint[1] * camera.image_height / img_scale
-    p = p * camD
-    K = torch.tensor([camera.fx / img_scale, 0, 0, camera.fy / img_scale]).reshape(2, 2)
-    Kinv = torch.inverse(K).to(torch.float32).to(device)
-    p = p @ Kinv.t()
-    camPos = torch.cat([p, camD], -1)
-    p = torch.nn.functional.pad(camPos[None], [0, 0, 1, 1, 1, 1], mode="replicate")
-    mask = torch.nn.functional.pad(mask[None].to(torch.float32), [0, 0, 1, 1, 1, 1], mode="replicate").to(torch.bool)
-    p_c = p[:, 1:-1, 1:-1, :] * mask[:, 1:-1, 1:-1, :]
-    p_u = (p[:, :-2, 1:-1, :] - p_c) * mask[:, :-2, 1:-1, :]
-    p_l = (p[:, 1:-1, :-2, :] - p_c) * mask[:, 1:-1, :-2, :]
-    p_b = (p[:, 2:, 1:-1, :] - p_c) * mask[:, 2:, 1:-1, :]
-    p_r = (p[:, 1:-1, 2:, :] - p_c) * mask[:, 1:-1, 2:, :]
-    n = (torch.linalg.cross(p_u, p_l) + torch.linalg.cross(p_r, p_u) + torch.linalg.cross(p_b, p_r)
-         + torch.linalg.cross(p_l, p_b))[0]
-    mask = mask[0, 1:-1, 1:-1, :]
-    n = torch.nn.functional.normalize(n, dim=-1)
-    return (n * mask).permute([2, 0, 1])
+from . import _lib as L
+from .imgops import depth2normal, exposure_affine
 
 
 # ---- spawn_gaussians (GR:469-778) ------------------------------------------------------------------
+# The elementwise epilogue between the five decoder heads and the rasterizer (activations, quaternion rotate /
+# multiply of utils/tools.py:743-751,811-844, view-direction transform, colour residual, alpha > 0 compaction) runs
+# as three CUDA kernels behind the C-ABI (pings_b200/csrc/pg_spawn.cuh): one gather before the heads, one fused
+# epilogue after them (single-pass ordered compaction, device-side count), and their adjoints.
+def _stream(dev) -> int:
+    return torch.cuda.current_stream(dev).cuda_stream
+
+
+class _SpawnPrepare(torch.autograd.Function):
+    """(geo_feature [N+1,Fg], color_feature [N+1,Fc]) -> decoder inputs of the n spawning points:
+    geo_in [n,Fg], color_in [n,Fc(+3 view direction in the point frame)]  (GR:563-569,587-597,690-698)."""
+
+    @staticmethod
+    def forward(ctx, geo_feature, color_feature, sidx, n, position, orientation, cam_origin, view_concat, xy_only):
+        lib = L.lib()
+        dev = geo_feature.device
+        gf, cf = geo_feature.detach().contiguous(), color_feature.detach().contiguous()
+        Fg, Fc = gf.shape[1], cf.shape[1]
+        use_view = bool(view_concat and cam_origin is not None)
+        geo_in = torch.empty(n, Fg, dtype=torch.float32, device=dev)
+        color_in = torch.empty(n, Fc + (3 if use_view else 0), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            L.check(lib.pg_spawn_prepare(n, L.ptr(sidx), L.ptr(position), L.ptr(orientation), L.ptr(cam_origin),
+                                         gf.data_ptr(), Fg, cf.data_ptr(), Fc, 0, int(use_view), int(bool(xy_only)),
+                                         geo_in.data_ptr(), color_in.data_ptr(), _stream(dev)), "spawn prepare")
+        ctx.sidx, ctx.n = sidx, n
+        ctx.shapes = (geo_feature.shape, color_feature.shape)
+        return geo_in, color_in
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, d_geo_in, d_color_in):
+        lib = L.lib()
+        gshape, cshape = ctx.shapes
+        outs = [None, None]
+        for k, (d, shape) in enumerate(((d_geo_in, gshape), (d_color_in, cshape))):
+            if d is None or not ctx.needs_input_grad[k]:
+                continue
+            d = d.contiguous()
+            g = torch.zeros(shape, dtype=torch.float32, device=d.device)
+            with torch.cuda.device(d.device):
+                L.check(lib.pg_spawn_prepare_backward(ctx.n, L.ptr(ctx.sidx), d.data_ptr(), d.shape[1], shape[1],
+                                                      g.data_ptr(), _stream(d.device)), "spawn prepare backward")
+            outs[k] = g
+        return outs[0], outs[1], None, None, None, None, None, None, None
+
+
+class _SpawnEpilogue(torch.autograd.Function):
+    """Raw outputs of the five heads -> (xyz, scale, rot, alpha, color) of the kept Gaussians + dense alpha_all."""
+
+    @staticmethod
+    def forward(ctx, xyz_raw, rot_raw, scale_raw, alpha_raw, color_raw, c):
+        lib = L.lib()
+        dev = xyz_raw.device
+        raws = [t.detach().to(torch.float32).contiguous() for t in (xyz_raw, rot_raw, scale_raw, alpha_raw, color_raw)]
+        n, K = c["n"], c["K"]
+        NK = n * K
+        a = L.PgSpawnArgs()
+        a.n, a.K = n, K
+        a.sidx, a.position, a.orientation = L.ptr(c["sidx"]), c["position"].data_ptr(), c["orientation"].data_ptr()
+        a.color, a.cam_origin = L.ptr(c["color"]), L.ptr(c["cam_origin"])
+        a.xyz_raw, a.rot_raw, a.scale_raw, a.alpha_raw, a.color_raw = [t.data_ptr() for t in raws]
+        a.disp_range, a.unit_scale, a.max_scale = c["disp_range"], c["unit_scale"], c["max_scale"]
+        a.z_far, a.scale_filter = c["z_far"], c["scale_filter"]
+        a.surfel, a.residual, a.alpha_filter, a.xy_only = c["surfel"], c["residual"], c["alpha_filter"], c["xy_only"]
+        f32 = dict(dtype=torch.float32, device=dev)
+        xyz, scale, rot = torch.empty(NK, 3, **f32), torch.empty(NK, 3, **f32), torch.empty(NK, 4, **f32)
+        alpha, color, alpha_all = torch.empty(NK, 1, **f32), torch.empty(NK, 3, **f32), torch.empty(NK, 1, **f32)
+        cpos = torch.empty(NK, dtype=torch.int32, device=dev)
+        free_out = torch.empty(NK, dtype=torch.uint8, device=dev) if c["free_mask"] is not None else None
+        state = torch.empty(lib.pg_spawn_state_words(NK), dtype=torch.int32, device=dev)
+        o = L.PgSpawnOut()
+        o.xyz, o.scale, o.rot, o.alpha, o.color = (t.data_ptr() for t in (xyz, scale, rot, alpha, color))
+        o.alpha_all, o.cpos, o.free_out, o.free_mask = alpha_all.data_ptr(), cpos.data_ptr(), L.ptr(free_out), L.ptr(c["free_mask"])
+        o.state = state.data_ptr()
+        with torch.cuda.device(dev):
+            L.check(lib.pg_spawn_epilogue_forward(C.byref(a), C.byref(o), _stream(dev)), "spawn epilogue")
+        ci = lib.pg_spawn_count_index(NK)
+        host = state[ci:ci + 2].cpu()    # the one host read of spawn_gaussians: kept count + NaN flag (GR:305-306 assert)
+        M, nan_flag = int(host[0]), int(host[1])
+        assert nan_flag == 0, "NaN in rotation"
+        ctx.args, ctx.keep = a, (raws, c, cpos)
+        ctx.NK = NK
+        outs = (xyz[:M], scale[:M], rot[:M], alpha[:M], color[:M], alpha_all)
+        fm = free_out[:M].view(torch.bool) if free_out is not None else None
+        if fm is not None:
+            ctx.mark_non_differentiable(cpos, fm)
+        else:
+            ctx.mark_non_differentiable(cpos)
+        return (*outs, cpos, fm)
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, d_xyz, d_scale, d_rot, d_alpha, d_color, d_alpha_all, _cpos, _fm):
+        lib = L.lib()
+        raws, c, cpos = ctx.keep
+        dev = cpos.device
+        K, n, NK = c["K"], c["n"], ctx.NK
+        cont = lambda t: None if t is None else t.to(torch.float32).contiguous()
+        d_xyz, d_scale, d_rot, d_alpha, d_color, d_alpha_all = map(cont, (d_xyz, d_scale, d_rot, d_alpha, d_color, d_alpha_all))
+        f32 = dict(dtype=torch.float32, device=dev)
+        g_xyz, g_rot, g_scale = torch.empty(n, 3 * K, **f32), torch.empty(n, 4 * K, **f32), torch.empty(n, 3 * K, **f32)
+        g_alpha, g_color = torch.empty(n, K, **f32), torch.empty(n, 3 * K, **f32)
+        g = L.PgSpawnGrads()
+        g.d_xyz, g.d_scale, g.d_rot, g.d_alpha, g.d_color = (L.ptr(t) for t in (d_xyz, d_scale, d_rot, d_alpha, d_color))
+        g.d_alpha_all, g.cpos = L.ptr(d_alpha_all), cpos.data_ptr()
+        g.d_xyz_raw, g.d_rot_raw, g.d_scale_raw = g_xyz.data_ptr(), g_rot.data_ptr(), g_scale.data_ptr()
+        g.d_alpha_raw, g.d_color_raw = g_alpha.data_ptr(), g_color.data_ptr()
+        with torch.cuda.device(dev):
+            L.check(lib.pg_spawn_epilogue_backward(C.byref(ctx.args), C.byref(g), _stream(dev)), "spawn epilogue backward")
+        return g_xyz, g_rot, g_scale, g_alpha, g_color, None
+
+
 def spawn_gaussians(neural_points_data: Dict, decoders: Dict, visible_mask: Optional[torch.Tensor] = None,
                     cam_origin: Optional[torch.Tensor] = None, dist_concat_on: bool = False,
                     view_concat_on: bool = False, alpha_filter_on: bool = True, scale_filter_on: bool = False,
@@ -86,11 +149,13 @@ def spawn_gaussians(neural_points_data: Dict, decoders: Dict, visible_mask: Opti
     color = neural_points_data.get("color")
     geo_features = neural_points_data["geo_feature"]
     color_features = neural_points_data["color_feature"]
-    resolution = neural_points_data["resolution"]
+    resolution = float(neural_points_data["resolution"])
     free_mask = neural_points_data.get("free_mask")
     valid_mask = neural_points_data.get("valid_mask")
-    stability = neural_points_data.get("stability")
-    gaussian_free_mask = None
+    if gs_type == "2d_gs":
+        raise NotImplementedError("2d_gs: diff_surfel_rasterization is not vendored by the reference (SURVEY.md 0.5)")
+    if not position.is_cuda:
+        raise RuntimeError("pings_b200.spawn_gaussians: expected CUDA tensors (there is no CPU fallback)")
 
     spawn_mask = None
     if visible_mask is not None and valid_mask is not None:
@@ -99,110 +164,58 @@ def spawn_gaussians(neural_points_data: Dict, decoders: Dict, visible_mask: Opti
         spawn_mask = visible_mask
     elif valid_mask is not None:
         spawn_mask = valid_mask
-    if spawn_mask is not None:
-        # One nonzero (one host sync) and index_select gathers instead of a boolean-mask index per tensor
-        # (GR:556-569 indexes each tensor with the mask: same rows, same order; every mask index costs a
-        # nonzero + a sync forward and a sort-based index_put backward).
-        sidx = torch.nonzero(spawn_mask).view(-1)
-        position = position.index_select(0, sidx)
-        orientation = orientation.index_select(0, sidx)
-        if color is not None:
-            color = color.index_select(0, sidx)
-        if free_mask is not None:
-            free_mask = free_mask.index_select(0, sidx)
-        if stability is not None:
-            stability = stability.index_select(0, sidx)
-        # index list padded with -1 = the trailing padding row of the feature tables, GR:563-569 / quirk q19
-        visible_idx = torch.cat((sidx, sidx.new_full((1,), geo_features.shape[0] - 1)))
-        geo_features = geo_features.index_select(0, visible_idx)
-        color_features = color_features.index_select(
-            0, torch.cat((sidx, sidx.new_full((1,), color_features.shape[0] - 1))))
-    if position.shape[0] < 10:
+    # the spawning points are addressed through an index list (the kernels gather; GR:556-569 materialises every
+    # masked tensor): one nonzero, i.e. one host read for the row count
+    sidx = torch.nonzero(spawn_mask).view(-1) if spawn_mask is not None else None
+    n_pts = int(sidx.shape[0]) if sidx is not None else int(position.shape[0])
+    if n_pts < 10:
         return None
 
     xyz_mlp, scale_mlp, rot_mlp = decoders["gauss_xyz"], decoders["gauss_scale"], decoders["gauss_rot"]
     alpha_mlp, color_mlp = decoders["gauss_alpha"], decoders["gauss_color"]
-    n_pts = position.shape[0]
-
-    view_direction = view_distance = None
-    if cam_origin is not None:
-        cam_origin = cam_origin.float()
-        view_direction = position - cam_origin
-        if view_direction_xy_only:
-            view_direction[:, -1] = 0
-        view_distance = view_direction.norm(dim=1, keepdim=True)
-        view_direction = view_direction / view_distance
-
-    geo_in = geo_features[:-1]
-    disp_range = displacement_range_ratio * resolution * torch.ones((n_pts, 1)).to(position)
-    xyz_disp = disp_range * torch.tanh(xyz_mlp.mlp_batch(geo_in))
     K = xyz_mlp.out_k
-    NK = n_pts * K
+    f32c = lambda t: None if t is None else t.detach().to(torch.float32).contiguous()
+    pos_c, quat_c, col_c = f32c(position), f32c(orientation), f32c(color)
+    cam_c = f32c(cam_origin)
+    geo_in, color_in = _SpawnPrepare.apply(geo_features, color_features, sidx, n_pts, pos_c, quat_c, cam_c,
+                                           bool(view_concat_on), bool(view_direction_xy_only))
+    xyz_raw = xyz_mlp.mlp_batch(geo_in)
+    rot_raw = rot_mlp.mlp_batch(geo_in)
+    scale_raw = scale_mlp.mlp_batch(geo_in)
+    alpha_in = geo_in
+    if dist_concat_on and cam_c is not None:   # GR:677-678: the view distance feeds the alpha head only
+        p_sel = pos_c if sidx is None else pos_c.index_select(0, sidx)
+        vd = p_sel - cam_c
+        if view_direction_xy_only:
+            vd = torch.cat((vd[:, :2], torch.zeros_like(vd[:, 2:])), 1)
+        alpha_in = torch.cat((geo_in, vd.norm(dim=1, keepdim=True)), dim=1)
+    alpha_raw = alpha_mlp.mlp_batch(alpha_in)
+    color_raw = color_mlp.mlp_batch(color_in)
 
     shifted_position = None
-    if record_shifted:
-        disp_all = xyz_disp.view(n_pts, 3, K)
+    if record_shifted:   # GR:614-626 (visualisation aid; note the reference's [n, 3, K] view of the [n, 3K] output)
+        disp_all = (displacement_range_ratio * resolution * torch.tanh(xyz_raw.detach())).view(n_pts, 3, K)
         max_disp, max_idx = torch.max(torch.norm(disp_all, dim=1), dim=1)
         disp_max = torch.gather(disp_all, dim=2, index=max_idx.unsqueeze(1).expand(-1, 3).unsqueeze(2)).squeeze(2)
         flag = max_disp > 2.0 * resolution
-        shifted_position = position[flag] + disp_max[flag]
+        p_sel = pos_c if sidx is None else pos_c.index_select(0, sidx)
+        shifted_position = p_sel[flag] + disp_max[flag]
 
-    point_quat = orientation.repeat(1, K).view(NK, -1)
-    xyz_disp = apply_quaternion_rotation(point_quat, xyz_disp.view(NK, -1))
-    gaussian_xyz = position.repeat(1, K).view(NK, -1) + xyz_disp
-
-    gaussian_rot = rot_mlp.mlp_batch(geo_in).view(NK, -1)
-    gaussian_rot = torch.nan_to_num(torch.nn.functional.normalize(gaussian_rot), 0, 0)
-    gaussian_rot = quat_multiply(point_quat, gaussian_rot)
-
-    dist_ratio = 0.0
-    if view_distance is not None and dist_adaptive_scale:
-        dist_ratio = (view_distance / z_far).repeat(1, scale_mlp.mlp_out_dim)
-    gaussian_scale = unit_scale_ratio * resolution * torch.exp(scale_mlp.mlp_batch(geo_in) + dist_ratio)
-    gaussian_scale = torch.clamp(gaussian_scale, max=max_scale_ratio * resolution).view(NK, -1)
-    if gs_type == "gaussian_surfel":
-        thin = torch.full((NK, 1), 1e-7).to(gaussian_scale)
-        gaussian_scale = torch.cat((gaussian_scale[:, :2], thin), dim=1)
-    elif gs_type == "2d_gs":
-        gaussian_scale = gaussian_scale[:, :2]
-
-    if dist_concat_on and view_distance is not None:
-        geo_in = torch.concat((geo_in, view_distance), dim=1)
-    gaussian_alpha = torch.tanh(alpha_mlp.mlp_batch(geo_in)).view(NK, -1)
-
-    color_in = color_features[:-1]
-    if view_concat_on and view_direction is not None:
-        view_direction = apply_quaternion_rotation(quat_inverse(orientation), view_direction)
-        color_in = torch.concat((color_in, view_direction), dim=1)
-    if learn_color_residual and color is not None:
-        residual = 0.1 * torch.tanh(color_mlp.mlp_batch(color_in))
-        gaussian_color = torch.clamp(color.repeat(1, K) + residual, 0.0, 1.0)
-    else:
-        gaussian_color = torch.sigmoid(color_mlp.mlp_batch(color_in))
-    gaussian_color = gaussian_color.view(NK, -1)
-
-    alpha_all = gaussian_alpha.clone()
-    if free_mask is not None:
-        gaussian_free_mask = free_mask.repeat(1, K).view(-1)
-
-    def _keep(mask):
-        nonlocal gaussian_xyz, gaussian_scale, gaussian_rot, gaussian_alpha, gaussian_color, gaussian_free_mask
-        kidx = torch.nonzero(mask).view(-1)   # one compaction index for all six tensors (see above)
-        gaussian_xyz, gaussian_scale = gaussian_xyz.index_select(0, kidx), gaussian_scale.index_select(0, kidx)
-        gaussian_rot, gaussian_alpha = gaussian_rot.index_select(0, kidx), gaussian_alpha.index_select(0, kidx)
-        gaussian_color = gaussian_color.index_select(0, kidx)
-        if gaussian_free_mask is not None:
-            gaussian_free_mask = gaussian_free_mask.index_select(0, kidx)
-
-    if alpha_filter_on:
-        _keep(gaussian_alpha.squeeze(-1) > 0.0)
-    if scale_filter_on:
-        _keep(torch.any(gaussian_scale > scale_filter_ratio * resolution, dim=1))
-
+    consts = dict(n=n_pts, K=int(K), sidx=sidx, position=pos_c, orientation=quat_c,
+                  color=col_c if learn_color_residual else None, cam_origin=cam_c,
+                  disp_range=float(displacement_range_ratio * resolution), unit_scale=float(unit_scale_ratio * resolution),
+                  max_scale=float(max_scale_ratio * resolution),
+                  z_far=float(z_far) if (dist_adaptive_scale and cam_c is not None) else -1.0,
+                  scale_filter=float(scale_filter_ratio * resolution) if scale_filter_on else -1.0,
+                  surfel=int(gs_type == "gaussian_surfel"), residual=int(bool(learn_color_residual and color is not None)),
+                  alpha_filter=int(bool(alpha_filter_on)), xy_only=int(bool(view_direction_xy_only)),
+                  free_mask=None if free_mask is None else free_mask.detach().contiguous().view(torch.uint8))
+    fn_out = _SpawnEpilogue.apply(xyz_raw, rot_raw, scale_raw, alpha_raw, color_raw, consts)
+    g_xyz, g_scale, g_rot, g_alpha, g_color, alpha_all, cpos, gaussian_free_mask = fn_out
     return {
-        "gaussian_xyz": gaussian_xyz, "gaussian_scale": gaussian_scale, "gaussian_rot": gaussian_rot,
-        "gaussian_alpha": gaussian_alpha, "gaussian_color": gaussian_color, "alpha_all": alpha_all,
-        "gaussian_free_mask": gaussian_free_mask, "local_view_gaussian_count": gaussian_xyz.shape[0],
+        "gaussian_xyz": g_xyz, "gaussian_scale": g_scale, "gaussian_rot": g_rot,
+        "gaussian_alpha": g_alpha, "gaussian_color": g_color, "alpha_all": alpha_all,
+        "gaussian_free_mask": gaussian_free_mask, "local_view_gaussian_count": g_xyz.shape[0],
         "shifted_position": shifted_position,
     }
 
@@ -310,7 +323,10 @@ def render(viewpoint_camera, cam_pose: Optional[torch.Tensor], neural_points_dat
         screenspace_points.retain_grad()
     except Exception:
         pass
-    assert not bool(torch.isnan(rotations).any()), "NaN in rotation"
+    # GR:305-306 asserts that no rotation is NaN: the spawned ones were checked inside the fused epilogue (its flag
+    # travels with the kept count), the frozen surrounding ones are checked here only when present
+    if gaussians is not None and gaussians["gaussian_xyz"].shape[0] > 10:
+        assert not bool(torch.isnan(gaussians["gaussian_rot"]).any()), "NaN in rotation"
 
     if gs_type == "gaussian_surfel":
         image, normal, depth, alpha, radii, contributions = rasterizer(
@@ -318,7 +334,7 @@ def render(viewpoint_camera, cam_pose: Optional[torch.Tensor], neural_points_dat
             rotations=rotations, theta=viewpoint_camera.cam_rot_delta, rho=viewpoint_camera.cam_trans_delta)
         alpha_d = alpha.detach()
         mask_vis = alpha_d > min_alpha
-        d2n = depth2normal(depth, mask_vis, viewpoint_camera, img_scale=img_scale) * alpha_d if d2n_on else None
+        d2n = depth2normal(depth, mask_vis, viewpoint_camera, img_scale=img_scale, alpha=alpha_d) if d2n_on else None
         results.update({"rend_normal": normal, "surf_depth": depth, "rend_alpha": alpha, "surf_normal": d2n,
                         "rend_dist": None, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
                         "radii": radii, "contributions": contributions})
@@ -330,7 +346,7 @@ def render(viewpoint_camera, cam_pose: Optional[torch.Tensor], neural_points_dat
         mask_vis = alpha_d > min_alpha
         # GR:426-437: depth / alpha where visible, 0 elsewhere (the reference edits the tensor in place)
         depth = torch.where(mask_vis, depth / torch.where(mask_vis, alpha_d, torch.ones_like(alpha_d)), depth)
-        d2n = depth2normal(depth, mask_vis, viewpoint_camera, img_scale=img_scale) * alpha_d if d2n_on else None
+        d2n = depth2normal(depth, mask_vis, viewpoint_camera, img_scale=img_scale, alpha=alpha_d) if d2n_on else None
         depth = torch.where(mask_vis, depth, torch.zeros_like(depth))
         results.update({"rend_normal": None, "surf_depth": depth, "rend_alpha": alpha, "surf_normal": d2n,
                         "rend_dist": None, "viewspace_points": screenspace_points, "visibility_filter": radii > 0,
@@ -338,10 +354,7 @@ def render(viewpoint_camera, cam_pose: Optional[torch.Tensor], neural_points_dat
 
     if correct_exposure:   # GR:449-462
         if correct_exposure_affine:
-            shp = image.shape
-            flat = image.permute(1, 2, 0).reshape(-1, 3)
-            flat = flat @ viewpoint_camera.exposure_mat.T + viewpoint_camera.exposure_offset
-            image = flat.view(shp[1], shp[2], 3).permute(2, 0, 1)
+            image = exposure_affine(image, viewpoint_camera.exposure_mat, viewpoint_camera.exposure_offset)
         else:
             image = torch.exp(viewpoint_camera.exposure_a) * image + viewpoint_camera.exposure_b
     results.update({"render": image})
