@@ -698,14 +698,16 @@ def surfel_leg(args, local) -> dict:
 
 
 # ----------------------------------------------------------------------------------------------
-# Config C4 (BASELINE.json configs[3]): one PINGS mapping step with the KITTI-GS decoder shapes
-# (config/run_kitti_gs.yaml:21-30: feature_dim 32, color_feature_dim 16, gs_mlp_hidden_dim 128, 8 Gaussians per
-# neural point, view_concat_on, learn_color_residual): render() = spawn_gaussians (5 decoder heads) + surfel
-# rasterizer, photometric L1 + fused-SSIM + depth L1 loss, backward to the neural-point features and decoder
-# weights, plus the SDF branch (query_feature + geo decoder on bs / world rows).  The 8 views of a batch are sharded
-# one per rank (weak scaling: one view per GPU per step); the exchange step is ONE all-reduce of the flat
-# [geo features | colour features | decoder weights] gradient buffer.  Reported under extra.mapping_step.
-C4 = dict(N=60_000, Fg=32, Fc=16, hidden=128, level=1, K=8, W=1226, H=370, res=0.4, sdf_bs=16384, seed=5)
+# Config C4 (BASELINE.json configs[3]; SURVEY.md §8d recipe, utils/mapper.py:995-1146): one PINGS mapping step on a
+# synthetic KITTI-shaped LiDAR + RGB frame.  Map = the mirror's update() (pinned to the reference's on a golden,
+# tests/test_maintenance_cpu.py) of ONE C1-style scan coloured by a procedural texture at voxel_size_m 0.25
+# (config/run_kitti_gs.yaml:21-30: feature_dim 32, color_feature_dim 16, weighted_first False, gs_mlp_hidden_dim 128,
+# view_concat, colour residual, 8 surfels per neural point).  A step = the 8-view batch (cameras along a 4 m straight
+# path, each 1226x370): per view render() + RGB L1 / fused-SSIM / depth loss + backward; one SDF batch of 8192 rows
+# ([N,6,35] -> 64 -> 1, sdf = sum_k w_k sdf_k); ONE flat gradient all-reduce; one fused AdamW step on the flat
+# parameter buffer.  The 8 views are SHARDED views[rank::world] (strong scaling), the SDF rows bs/world per rank;
+# replicated parameters are checked bit-identical across ranks after the last step.
+C4 = dict(Fg=32, Fc=16, hidden=128, level=1, K=8, W=1226, H=370, res=0.25, sdf_bs=8192, views=8, seed=2, lr=1e-3)
 
 
 class _ViewCam(SimpleNamespace):
@@ -715,23 +717,19 @@ class _ViewCam(SimpleNamespace):
                             device=self.device)
 
 
-def mapping_leg(args, local, world, rank) -> dict:
+def _c4_view(i: int, dev):
+    """Camera i of the batch: at (0.5 i, 0, 0) m looking along +x (LiDAR frame: x forward, z up)."""
     import math
-    from pings_b200 import synth, synth_neural as SN
-    from pings_b200.decoder import Decoder
-    from pings_b200.fused_ssim import fused_ssim
-    from pings_b200.gaussian_renderer import render
-    from pings_b200.neural_points import default_config
-    from pings_b200.parallel import FlatGradAllReduce, shard_rows
-    dev = torch.device("cuda", local)
-    N, Fg, Fc, Hd, Lv, K, W, H = (C4[k] for k in ("N", "Fg", "Fc", "hidden", "level", "K", "W", "H"))
-    g = torch.Generator().manual_seed(C4["seed"])
-    cam0 = synth.kitti_camera(C4["seed"], W, H)
-    T = cam0.T_wc.clone()
-    T[:3, 3] += T[:3, 2] * (0.1 * rank)          # this rank's view of the batch
-    cam = synth.Camera(cam0.W, cam0.H, cam0.fx, cam0.fy, cam0.cx, cam0.cy, T)
+    from pings_b200 import synth
+    W, H = C4["W"], C4["H"]
+    T = torch.eye(4, dtype=torch.float64)
+    T[:3, 0] = torch.tensor([0.0, -1.0, 0.0], dtype=torch.float64)   # camera x (right)  = -y world
+    T[:3, 1] = torch.tensor([0.0, 0.0, -1.0], dtype=torch.float64)   # camera y (down)   = -z world
+    T[:3, 2] = torch.tensor([1.0, 0.0, 0.0], dtype=torch.float64)    # camera z (forward) = +x world
+    T[:3, 3] = torch.tensor([4.0 * i / (C4["views"] - 1), 0.0, 0.0], dtype=torch.float64)
+    cam = synth.Camera(W, H, 718.856, 718.856, 607.19, 185.22, T)
     view, full, proj, center = [m.to(dev) for m in cam.matrices()]
-    vc = _ViewCam(device=dev, uid=rank, image_width=W, image_height=H, FoVx=2 * math.atan(cam.tanfovx),
+    vc = _ViewCam(device=dev, uid=i, image_width=W, image_height=H, FoVx=2 * math.atan(cam.tanfovx),
                   FoVy=2 * math.atan(cam.tanfovy), zfar=100.0, fx=cam.fx, fy=cam.fy,
                   prcppoint=torch.tensor([cam.cx / W, cam.cy / H], device=dev), projection_matrix=proj,
                   world_view_transform=view, full_proj_transform=full, camera_center=center,
@@ -740,84 +738,124 @@ def mapping_leg(args, local, world, rank) -> dict:
                   exposure_mat=torch.eye(3, device=dev).requires_grad_(True),
                   exposure_offset=torch.zeros(1, 3, device=dev).requires_grad_(True),
                   exposure_a=torch.zeros(1, device=dev), exposure_b=torch.zeros(1, device=dev))
-    # neural points on "surfaces" in front of camera 0: log-uniform depth 3..60 m inside the frustum (same on every rank)
-    z = torch.exp(torch.rand(N, generator=g) * (math.log(60.0) - math.log(3.0)) + math.log(3.0))
-    x = (torch.rand(N, generator=g) - 0.5) * 2.1 * cam0.tanfovx * z
-    y = (torch.rand(N, generator=g) - 0.5) * 2.1 * cam0.tanfovy * z
-    pc = torch.stack([x, y, z, torch.ones(N)], 1).double()
-    pos = (cam0.T_wc @ pc.T).T[:, :3].float().to(dev)
-    quat = torch.zeros(N, 4)
-    quat[:, 0] = 1.0
-    data = {"position": pos, "orientation": quat.to(dev), "color": torch.rand(N, 3, generator=g).to(dev),
-            "geo_feature": (0.1 * torch.randn(N + 1, Fg, generator=g)).to(dev).requires_grad_(True),
-            "color_feature": (0.1 * torch.randn(N + 1, Fc, generator=g)).to(dev).requires_grad_(True),
-            "resolution": C4["res"]}
-    cfg = default_config(device=dev)
+    g = torch.Generator().manual_seed(900 + i)
+    target = torch.rand(3, H, W, generator=g).to(dev)
+    target_d = (torch.rand(1, H, W, generator=g) * 40 + 3).to(dev)
+    return vc, target, target_d
+
+
+def mapping_leg(args, local, world, rank) -> dict:
+    from pings_b200 import synth_neural as SN
+    from pings_b200.decoder import Decoder
+    from pings_b200.fused_ssim import fused_ssim
+    from pings_b200.gaussian_renderer import render
+    from pings_b200.losses import photo_depth_loss
+    from pings_b200.neural_points import NeuralPoints, default_config
+    from pings_b200.parallel import FlatAdamW, FlatGradAllReduce, replicas_in_sync, shard_rows, shard_views
+    dev = torch.device("cuda", local)
+    Fg, Fc, Hd, Lv, K, W, H = (C4[k] for k in ("Fg", "Fc", "hidden", "level", "K", "W", "H"))
+    # ---- map: one coloured scan through update() (identical on every rank) ----
+    g = torch.Generator().manual_seed(C4["seed"])
+    pts = SN.lidar_scan(C4["seed"])
+    cols = (0.5 + 0.5 * torch.sin(pts * torch.tensor([0.7, 1.1, 2.3]))).clamp(0, 1)    # procedural texture
+    cfg = default_config(device=dev, voxel_size_m=C4["res"], search_alpha=0.8, feature_dim=Fg, color_feature_dim=Fc,
+                         color_on=True, weighted_first=False, buffer_size=int(2e7), track_on=False,
+                         temporal_local_map_off=True)
+    npm = NeuralPoints(cfg)
+    npm.travel_dist = torch.zeros(1, device=dev)
+    npm.update(pts.to(dev), cols.to(dev), None, torch.zeros(3, device=dev), None, 0)
+    n = npm.count()
+    npm.geo_features = (0.1 * torch.randn(n + 1, Fg, generator=g)).to(dev)
+    npm.color_features = (0.1 * torch.randn(n + 1, Fc, generator=g)).to(dev)
+    npm.reset_local_map(torch.zeros(3, device=dev), None, 0)
     torch.manual_seed(C4["seed"])                  # identical decoder weights on every rank
     decs = {"gauss_xyz": Decoder(cfg, Fg, Hd, Lv, 3, K, 0), "gauss_rot": Decoder(cfg, Fg, Hd, Lv, 4, K, 0),
             "gauss_scale": Decoder(cfg, Fg, Hd, Lv, 3, K, 0), "gauss_alpha": Decoder(cfg, Fg, Hd, Lv, 1, K, 0),
             "gauss_color": Decoder(cfg, Fc, Hd, Lv, 3, K, 3)}
-    for d in decs.values():
+    sdf_dec = Decoder(cfg, Fg, 64, 1, 1)
+    for d in list(decs.values()) + [sdf_dec]:
         d.to(dev)
-    # SDF branch: the PIN-SLAM shaped map / geo decoder of the C1 leg, bs rows split over the ranks
-    npm, sdf_dec, q = SN.c1_map_and_queries(device=dev)
+    data = {"position": npm.local_neural_points, "orientation": npm.local_point_orientations,
+            "color": npm.local_point_colors, "geo_feature": npm.local_geo_features,
+            "color_feature": npm.local_color_features, "resolution": C4["res"],
+            "free_mask": npm.local_free_gs_mask, "valid_mask": npm.local_valid_gs_mask}
+    my_views = [_c4_view(i, dev) for i in shard_views(list(range(C4["views"])), rank, world)]
+    q_all = (pts + 0.05 * torch.randn(pts.shape, generator=g))[torch.randperm(pts.shape[0], generator=g)[:C4["sdf_bs"]]]
     lo, hi = shard_rows(C4["sdf_bs"], rank, world)
-    qb = q[lo:hi].clone()
+    qb = q_all[lo:hi].contiguous().to(dev)
     sdf_target = torch.zeros(hi - lo, device=dev)
-    gt = torch.Generator().manual_seed(91 + rank)
-    target = torch.rand(3, H, W, generator=gt).to(dev)
-    target_d = (torch.rand(1, H, W, generator=gt) * 40 + 3).to(dev)
     bg = torch.zeros(3, device=dev)
-    params = [data["geo_feature"], data["color_feature"], npm.local_geo_features]
+    params = [npm.local_geo_features, npm.local_color_features]
     for d in list(decs.values()) + [sdf_dec]:
         params += [p for p in d.parameters()]
-    exchange = FlatGradAllReduce(params, average=True)
+    exchange = FlatGradAllReduce(params, average=False)
+    opt = FlatAdamW(exchange, lr=C4["lr"])
     info = {}
+    nv = float(C4["views"])
 
     def step():
         exchange.attach()   # grads are views of the flat exchange buffer, zeroed: no pack / scatter copies
-        for p in (vc.cam_rot_delta, vc.cam_trans_delta, vc.exposure_mat, vc.exposure_offset):
-            p.grad = None
-        res = render(vc, None, data, decs, None, bg, view_concat_on=True, learn_color_residual=True,
-                     gs_type="gaussian_surfel", d2n_on=False)
-        rgb = res["render"]
-        loss = 0.8 * (rgb - target).abs().mean() + 0.2 * (1.0 - fused_ssim(rgb.unsqueeze(0), target.unsqueeze(0)))
-        loss = loss + 0.05 * (res["surf_depth"] - target_d).abs().mean() + 0.01 * res["rend_alpha"].mean()
+        total = None
+        for vc, target, target_d in my_views:
+            for p in (vc.cam_rot_delta, vc.cam_trans_delta, vc.exposure_mat, vc.exposure_offset):
+                p.grad = None
+            res = render(vc, None, data, decs, None, bg, view_concat_on=True, learn_color_residual=True,
+                         gs_type="gaussian_surfel", d2n_on=False)
+            if res is None:
+                raise RuntimeError("render() returned None for a C4 view")
+            rgb = res["render"]
+            l1d, _, _ = photo_depth_loss(rgb, target, res["surf_depth"], target_d, res["rend_alpha"], 0.05, 0.5, 80.0, 1e-3)
+            loss = (0.8 * l1d + 0.2 * (1.0 - fused_ssim(rgb.unsqueeze(0), target.unsqueeze(0)))
+                    + 0.01 * res["rend_alpha"].mean()) / nv            # sum over the 8 views = mean loss of the batch
+            loss.backward()
+            total = loss.detach() if total is None else total + loss.detach()
+            info["gaussians"] = int(res["gaussian_xyz"].shape[0])
         geo, _, w, cnt, _ = npm.query_feature(qb, accumulate_stability=False)
-        loss = loss + 0.5 * (sdf_dec.sdf(geo) - sdf_target).abs().mean()
-        loss.backward()
-        exchange()
-        info["gaussians"] = int(res["gaussian_xyz"].shape[0])
-        return loss
+        sdf = (sdf_dec.sdf(geo) * w.squeeze(-1)).sum(1)               # weighted_first False: utils/mapper.py:2276-2279
+        l_sdf = 0.5 * (sdf - sdf_target).abs().sum() / C4["sdf_bs"]
+        l_sdf.backward()
+        exchange()          # ONE all-reduce (sum over ranks = the loss of the global batch)
+        opt.step()          # ONE fused AdamW launch on the flat parameter buffer
+        return total + l_sdf.detach()
 
+    if not _all_ok(len(my_views) > 0 or world > C4["views"], world, dev):
+        raise RuntimeError("C4 setup failed on a rank")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     steps, warm = max(3, min(args.steps, 10)), 3
     for _ in range(warm):
         step()
     barrier(world)
     evs = []
+    loss = None
     for _ in range(steps):
         flush.fill_(1)
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        step()
+        loss = step()
         b.record()
         evs.append((a, b))
     barrier(world)
+    in_sync = replicas_in_sync([opt.flat])
+    lt = loss.clone()
+    if world > 1:
+        dist.all_reduce(lt)            # every rank holds its share of the batch loss
     t = torch.tensor([sum(a.elapsed_time(b) for a, b in evs) / steps], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = float(t.item())
-    return {"mapping_step": {"metric": "PINGS mapping steps (views)/s: render() + loss + backward + SDF branch + exchange (C4)",
-                             "value": round(world / (ms * 1e-3), 2), "unit": "views/s", "ms_per_step": round(ms, 4),
-                             "mpix_per_s": round(world * W * H / (ms * 1e-3) / 1e6, 2),
-                             "neural_points": N, "gaussians_per_point": K, "gaussians_rendered": info.get("gaussians"),
-                             "decoder": f"{Fg}+0/{Fc}+3 -> {Hd} x{Lv} -> K*out (5 heads)", "sdf_rows_per_rank": hi - lo,
-                             "exchange_bytes": exchange.nbytes if world > 1 else 0,
-                             "note": "one view per GPU per step (a batch of `world` views), eager spawn_gaussians glue "
-                                     "included; host-driven, timed with CUDA events, L2 flushed between steps"}}
-
-
+    return {"mapping_step": {"metric": "PINGS mapping views/s: 8-view batch (render() + loss + backward) + SDF batch + "
+                                       "gradient all-reduce + fused AdamW (C4)",
+                             "value": round(C4["views"] / (ms * 1e-3), 2), "unit": "views/s", "ms_per_step": round(ms, 4),
+                             "views_per_step": C4["views"], "views_per_rank": len(my_views), "scaling": "strong",
+                             "mpix_per_s": round(C4["views"] * W * H / (ms * 1e-3) / 1e6, 2),
+                             "neural_points": int(n), "local_points": int(npm.local_count()), "gaussians_per_point": K,
+                             "gaussians_rendered_last_view": info.get("gaussians"),
+                             "decoder": f"{Fg}+0/{Fc}+3 -> {Hd} x{Lv} -> K*out (5 heads); SDF [N,6,{Fg + 3}] -> 64 -> 1",
+                             "sdf_rows_per_rank": hi - lo, "exchange_bytes": exchange.nbytes if world > 1 else 0,
+                             "loss_after_steps": round(float(lt), 6), "steps_run": steps + warm,
+                             "replicas_in_sync": bool(in_sync),
+                             "note": "map built by update() from one coloured C1-style scan at voxel 0.25 m; host-driven "
+                                     "step timed with CUDA events, L2 flushed between steps"}}
 
 # ----------------------------------------------------------------------------------------------
 # Config C5 (BASELINE.json configs[4]; reference caller inspect_pings.py:361 render_with_poses): 5M surfels, 64 novel

@@ -199,10 +199,8 @@ __global__ void __launch_bounds__(kSortThreads) radix_hist_kernel(
     }
   }
 #pragma unroll
-  for (int it = 0; it < kSortIpt; ++it) {
-    uint32_t peers = __match_any_sync(0xffffffffu, d[it]);
-    if (d[it] != 0xffffffffu && lane == (__ffs(peers) - 1)) atomicAdd(&h[d[it]], __popc(peers));
-  }
+  for (int it = 0; it < kSortIpt; ++it)
+    if (d[it] != 0xffffffffu) atomicAdd(&h[d[it]], 1u);
   __syncthreads();
   if (threadIdx.x < nbins) hist[threadIdx.x * nblk + blockIdx.x] = h[threadIdx.x];
 }
@@ -243,9 +241,7 @@ __global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(
   for (int it = 0; it < kSortIpt; ++it) {
     uint32_t i = base + it * 32 + lane;
     uint32_t d = (i < n && !(DROP && k[it] == (KeyT)~(KeyT)0)) ? ((uint32_t)(k[it] >> shift) & mask) : 0xffffffffu;
-    uint32_t peers = __match_any_sync(0xffffffffu, d);
-    if (d != 0xffffffffu && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
-    __syncwarp();
+    if (d != 0xffffffffu) atomicAdd(&wh[warp][d], 1u);
   }
   __syncthreads();
   // digit = threadIdx.x: CTA-local start of the digit (exclusive scan of the CTA's digit counts) and the distance
@@ -270,19 +266,25 @@ __global__ void __launch_bounds__(kSortThreads) radix_scatter_kernel(
   __syncthreads();
   const uint32_t lt = (1u << lane) - 1u;
   // exchange through shared memory so that the global stores go out in per-digit runs (see depth_sort_coop_kernel)
+  uint32_t peers[kSortIpt];
+#pragma unroll
+  for (int it = 0; it < kSortIpt; ++it) {   // 16 independent MATCH.ANY in flight (see depth_sort_coop_kernel)
+    const uint32_t i = base + it * 32 + lane;
+    const bool valid = i < n && !(DROP && k[it] == (KeyT)~(KeyT)0);
+    peers[it] = __match_any_sync(0xffffffffu, valid ? ((uint32_t)(k[it] >> shift) & mask) : 0xffffffffu);
+  }
 #pragma unroll
   for (int it = 0; it < kSortIpt; ++it) {
     uint32_t i = base + it * 32 + lane;
     bool valid = i < n && !(DROP && k[it] == (KeyT)~(KeyT)0);
     uint32_t d = valid ? ((uint32_t)(k[it] >> shift) & mask) : 0xffffffffu;
-    uint32_t peers = __match_any_sync(0xffffffffu, d);
     if (valid) {
-      const uint32_t slot = wh[warp][d] + __popc(peers & lt);
+      const uint32_t slot = wh[warp][d] + __popc(peers[it] & lt);
       sk[slot] = k[it];
       sv[slot] = v[it];
     }
     __syncwarp();
-    if (valid && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
+    if (valid && lane == (__ffs(peers[it]) - 1)) wh[warp][d] += __popc(peers[it]);
     __syncwarp();
   }
   __syncthreads();
@@ -408,16 +410,17 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
       k[it] = i < n ? __ldcg(kin + i) : 0xffffffffu;
       v[it] = i < n ? (pass == 0 ? i : __ldcg(vin + i)) : 0u;
     }
+    // counting: plain shared-memory atomics (no ranks needed here).  MATCH.ANY costs ~450 cycles per call on sm_100
+    // (one internal round per distinct digit in the warp; ncu source view of the previous version: the instructions
+    // consuming its result held 40 % of the stall samples), so it is used once per item per pass, for the ranks
+    // only, and all 16 calls are issued back to back there.
     uint32_t valid = 0;   // bit `it`: item takes part in this pass
 #pragma unroll
     for (int it = 0; it < kSortIpt; ++it) {
       const uint32_t i = base + it * 32 + lane;
       const bool ok = i < n && !(drop && k[it] == 0xffffffffu);
       valid |= ok ? (1u << it) : 0u;
-      const uint32_t d = ok ? ((k[it] >> shift) & 255u) : 0xffffffffu;
-      const uint32_t peers = __match_any_sync(0xffffffffu, d);
-      if (ok && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
-      __syncwarp();
+      if (ok) atomicAdd(&wh[warp][(k[it] >> shift) & 255u], 1u);
     }
     __syncthreads();
     {
@@ -434,15 +437,9 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
     {
       // digit = threadIdx.x: items of this digit in earlier blocks (group rows before mine + rows of the CTAs
       // before me in my group), and in all blocks
-      // (fully unrolled and predicated: up to 44 INDEPENDENT loads in flight; a counted loop serialises them on the
-      // L2 latency, ~0.7 us each)
       uint32_t below = 0;
-#pragma unroll
-      for (uint32_t g = 0; g < kSortMaxGroups; ++g)
-        if (g < grp) below += __ldcg(gsum + (size_t)g * 256 + threadIdx.x);
-#pragma unroll
-      for (uint32_t j = 0; j + 1 < kSortGroup; ++j)
-        if (grp * kSortGroup + j < blk) below += __ldcg(hist + (size_t)(grp * kSortGroup + j) * 256 + threadIdx.x);
+      for (uint32_t g = 0; g < grp; ++g) below += __ldcg(gsum + (size_t)g * 256 + threadIdx.x);
+      for (uint32_t b = grp * kSortGroup; b < blk; ++b) below += __ldcg(hist + (size_t)b * 256 + threadIdx.x);
       const uint32_t all = __ldcg(dtot + threadIdx.x);
       uint32_t tot;
       const uint32_t gstart = block_excl_scan_256(all, &tot) + below;   // global start of this CTA's items of the digit
@@ -466,18 +463,21 @@ __global__ void __launch_bounds__(kSortThreads) depth_sort_coop_kernel(const Dep
     // exchange through shared memory: items are placed at their CTA-local sorted slot first, so that the global
     // stores below go out in runs of one digit (16 consecutive items on average) instead of 4-byte scatters -
     // scattered 4-B stores cost a 32-B sector each and were the floor of the pass
+    uint32_t peers[kSortIpt];
+#pragma unroll
+    for (int it = 0; it < kSortIpt; ++it)   // 16 independent MATCH.ANY in flight
+      peers[it] = __match_any_sync(0xffffffffu, ((valid >> it) & 1u) ? ((k[it] >> shift) & 255u) : 0xffffffffu);
 #pragma unroll
     for (int it = 0; it < kSortIpt; ++it) {
       const bool ok = (valid >> it) & 1u;
-      const uint32_t d = ok ? ((k[it] >> shift) & 255u) : 0xffffffffu;
-      const uint32_t peers = __match_any_sync(0xffffffffu, d);
+      const uint32_t d = (k[it] >> shift) & 255u;
       if (ok) {
-        const uint32_t slot = wh[warp][d] + __popc(peers & lt);
+        const uint32_t slot = wh[warp][d] + __popc(peers[it] & lt);
         sk[slot] = k[it];
         sv[slot] = v[it];
       }
       __syncwarp();
-      if (ok && lane == (__ffs(peers) - 1)) wh[warp][d] += __popc(peers);
+      if (ok && lane == (__ffs(peers[it]) - 1)) wh[warp][d] += __popc(peers[it]);
       __syncwarp();
     }
     __syncthreads();

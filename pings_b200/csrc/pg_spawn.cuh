@@ -132,7 +132,12 @@ __global__ void __launch_bounds__(256) spawn_epilogue_kernel(SpawnArgs a, SpawnO
     }
     keep = !a.alpha_filter || oa > 0.f;                                        // GR:727-737
     if (a.scale_filter >= 0.f) keep = keep && (os[0] > a.scale_filter || os[1] > a.scale_filter || os[2] > a.scale_filter);
-    if (o.free_mask) fm = o.free_mask[src];
+    // GR:719-720: `free_mask.repeat(1, K).view(-1)` on the 1-D per-point mask TILES it (entry r <- point r mod n),
+    // it does not repeat each point K times; reproduced as is (parity quirk)
+    if (o.free_mask) {
+      const int64_t j = r % a.n;
+      fm = o.free_mask[a.sidx ? a.sidx[j] : j];
+    }
   }
   // ordered compaction: warp ballot -> block scan -> decoupled look-back over the blocks
   const uint32_t bal = __ballot_sync(0xffffffffu, keep);
@@ -215,9 +220,9 @@ __global__ void __launch_bounds__(256) spawn_epilogue_bwd_kernel(SpawnArgs a, Sp
       // adjoint of y -> q (*) y
       float dy[4];
       dy[0] = q.x * c.x + q.y * c.y + q.z * c.z + q.w * c.w;
-      dy[1] = -q.y * c.x + q.x * c.y - q.w * c.z + q.z * c.w;
-      dy[2] = -q.z * c.x + q.w * c.y + q.x * c.z - q.y * c.w;
-      dy[3] = -q.w * c.x - q.z * c.y + q.y * c.z + q.x * c.w;
+      dy[1] = -q.y * c.x + q.x * c.y + q.w * c.z - q.z * c.w;
+      dy[2] = -q.z * c.x - q.w * c.y + q.x * c.z + q.y * c.w;
+      dy[3] = -q.w * c.x + q.z * c.y - q.y * c.z + q.x * c.w;
       float v[4] = {a.rot_raw[4 * r], a.rot_raw[4 * r + 1], a.rot_raw[4 * r + 2], a.rot_raw[4 * r + 3]};
       const float n2 = sqrtf(v[0] * v[0] + v[1] * v[1] + v[2] * v[2] + v[3] * v[3]);
       if (n2 > 1e-12f) {   // y = v / |v|: d_v = (d_y - y (y . d_y)) / |v|

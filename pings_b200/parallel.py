@@ -128,6 +128,34 @@ class FlatGradAllReduce:
         self.wait()
 
 
+class FlatAdamW:
+    """The replicated-parameter update of a data-parallel step as ONE fused kernel (SURVEY.md §8e names it the serial
+    part of the C4 step; the reference builds a per-tensor AdamW in utils/tools.py:142 setup_optimizer).
+
+    The parameters are re-pointed at consecutive slices of one flat buffer (`p.data` becomes a view) that is itself
+    a leaf parameter whose `.grad` is the flat exchange buffer of a FlatGradAllReduce (attach() mode), so
+    `torch.optim.AdamW(fused=True)` sees a single tensor: one launch per step instead of one multi-tensor launch
+    over ~30 tensors plus their bookkeeping."""
+
+    def __init__(self, exchange: "FlatGradAllReduce", lr: float = 1e-3, weight_decay: float = 0.0, betas=(0.9, 0.999),
+                 eps: float = 1e-15):
+        self.exchange = exchange
+        flat = torch.empty_like(exchange.flat)
+        off = 0
+        for p, n in zip(exchange.params, exchange.sizes):
+            flat[off:off + n].copy_(p.data.reshape(-1))
+            p.data = flat[off:off + n].view(p.shape)
+            off += n
+        self.flat = torch.nn.Parameter(flat)
+        self.flat.grad = exchange.flat
+        fused = flat.is_cuda
+        self.opt = torch.optim.AdamW([self.flat], lr=lr, weight_decay=weight_decay, betas=betas, eps=eps, fused=fused)
+
+    def step(self) -> None:
+        self.flat.grad = self.exchange.flat
+        self.opt.step()
+
+
 def replicas_in_sync(tensors: Iterable[torch.Tensor], group=None) -> bool:
     """Debug check of DESIGN.md §6: replicated parameters must be bit-identical on every rank after a
     step.  Compares an int64 checksum of the raw bits (all-gather of one scalar per rank)."""
