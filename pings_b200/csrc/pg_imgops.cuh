@@ -132,11 +132,18 @@ __device__ __forceinline__ D2NStencil d2n_stencil(const D2NArgs& a, int x, int y
   s.ac = ray(x, y); s.au = ray(x, yu); s.al = ray(xl, y); s.ab = ray(x, yb); s.ar = ray(xr, y);
   s.mc = a.mask[ic] ? 1.f : 0.f; s.mu = a.mask[s.iu] ? 1.f : 0.f; s.ml = a.mask[s.il] ? 1.f : 0.f;
   s.mb = a.mask[s.ib] ? 1.f : 0.f; s.mr = a.mask[s.ir] ? 1.f : 0.f;
-  const V3 pc = v3mul(s.ac, a.depth[ic] * s.mc);
-  s.pu = v3mul(v3sub(v3mul(s.au, a.depth[s.iu]), pc), s.mu);
-  s.pl = v3mul(v3sub(v3mul(s.al, a.depth[s.il]), pc), s.ml);
-  s.pb = v3mul(v3sub(v3mul(s.ab, a.depth[s.ib]), pc), s.mb);
-  s.pr = v3mul(v3sub(v3mul(s.ar, a.depth[s.ir]), pc), s.mr);
+  // Back-projected points with explicitly rounded products, in the reference's order ((x - cx) * d) / fx: at an image
+  // border the replicated neighbour IS the centre pixel and their difference must be exactly zero (an FMA-contracted
+  // a*d - round(a*d) leaves a 1e-7 residue that the normalisation blows up to a unit vector).
+  auto point = [&](int xx, int yy, int idx) {
+    const float d = a.depth[idx];
+    return V3{__fmul_rn(__fmul_rn((float)xx - a.cx, d), a.inv_fx), __fmul_rn(__fmul_rn((float)yy - a.cy, d), a.inv_fy), d};
+  };
+  const V3 pc = v3mul(point(x, y, ic), s.mc);
+  s.pu = v3mul(v3sub(point(x, yu, s.iu), pc), s.mu);
+  s.pl = v3mul(v3sub(point(xl, y, s.il), pc), s.ml);
+  s.pb = v3mul(v3sub(point(x, yb, s.ib), pc), s.mb);
+  s.pr = v3mul(v3sub(point(xr, y, s.ir), pc), s.mr);
   return s;
 }
 

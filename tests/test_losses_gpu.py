@@ -55,3 +55,64 @@ def test_rgb_only_and_empty_mask():
     loss, _, l_d = photo_depth_loss(rgb, gt, depth, torch.zeros(1, 33, 47, device="cuda"), None, 0.5, 1.0, 2.0)
     loss.backward()
     assert float(l_d) == 0.0 and float(depth.grad.abs().max()) == 0.0
+
+
+# ---- depth2normal / exposure kernels (pings_b200/imgops.py) ------------------------------------------------------
+def _d2n_restatement(depth, mask, prcp, iw, ih, fx, fy, img_scale):
+    """TEST ORACLE: eager restatement of gaussian_splatting/utils/point_utils.py:83-148 (the numeric pin against the
+    reference itself is tests/golden/render_post.npz; this one adds autograd for the backward check)."""
+    camD = depth.permute([1, 2, 0])
+    m = mask.permute([1, 2, 0])
+    H, W, _ = camD.shape
+    h, w = torch.meshgrid(torch.arange(H, device=depth.device, dtype=torch.float32),
+                          torch.arange(W, device=depth.device, dtype=torch.float32), indexing="ij")
+    p = torch.stack([w - prcp[0] * iw / img_scale, h - prcp[1] * ih / img_scale], dim=-1) * camD
+    p = p / torch.tensor([fx / img_scale, fy / img_scale], device=depth.device)
+    cam = torch.cat([p, camD], -1)
+    pp = torch.nn.functional.pad(cam[None], [0, 0, 1, 1, 1, 1], mode="replicate")
+    mm = torch.nn.functional.pad(m[None].float(), [0, 0, 1, 1, 1, 1], mode="replicate")
+    pc = pp[:, 1:-1, 1:-1] * mm[:, 1:-1, 1:-1]
+    pu = (pp[:, :-2, 1:-1] - pc) * mm[:, :-2, 1:-1]
+    pl = (pp[:, 1:-1, :-2] - pc) * mm[:, 1:-1, :-2]
+    pb = (pp[:, 2:, 1:-1] - pc) * mm[:, 2:, 1:-1]
+    pr = (pp[:, 1:-1, 2:] - pc) * mm[:, 1:-1, 2:]
+    cr = torch.linalg.cross
+    n = (cr(pu, pl) + cr(pr, pu) + cr(pb, pr) + cr(pl, pb))[0]
+    n = torch.nn.functional.normalize(n, dim=-1)
+    return (n * mm[0, 1:-1, 1:-1]).permute([2, 0, 1])
+
+
+@pytest.mark.parametrize("H,W,scale", [(64, 96, 1), (37, 53, 2)])
+def test_depth2normal_and_exposure_kernels(H, W, scale):
+    from types import SimpleNamespace
+    from pings_b200.imgops import depth2normal, exposure_affine
+    g = torch.Generator().manual_seed(5)
+    depth = (torch.rand(1, H, W, generator=g) * 20 + 1).cuda().requires_grad_(True)
+    alpha = torch.rand(1, H, W, generator=g)
+    alpha[:, : H // 4] *= 5e-4
+    alpha = alpha.cuda()
+    mask = alpha > 1e-3
+    cam = SimpleNamespace(prcppoint=torch.tensor([0.48, 0.53]), image_width=W * scale, image_height=H * scale, fx=80.0, fy=75.0)
+    out = depth2normal(depth, mask, cam, img_scale=scale, alpha=alpha)
+    d2 = depth.detach().clone().requires_grad_(True)
+    ref = _d2n_restatement(d2, mask, [0.48, 0.53], W * scale, H * scale, 80.0, 75.0, scale) * alpha
+    bad = (out - ref).abs().amax(0) > 1e-4
+    assert int(bad.sum()) == 0, (int(bad.sum()), torch.nonzero(bad)[:8].tolist(), out[:, bad][:, :4].tolist(), ref[:, bad][:, :4].tolist())
+    torch.testing.assert_close(out, ref, rtol=1e-4, atol=1e-5)
+    w = torch.randn(3, H, W, generator=g).cuda()
+    (out * w).sum().backward()
+    (ref * w).sum().backward()
+    torch.testing.assert_close(depth.grad, d2.grad, rtol=1e-3, atol=1e-4 * float(d2.grad.abs().max()))
+    # affine exposure
+    img = torch.rand(3, H, W, generator=g).cuda().requires_grad_(True)
+    M = (torch.eye(3) + 0.1 * torch.randn(3, 3, generator=g)).cuda().requires_grad_(True)
+    off = (0.05 * torch.randn(1, 3, generator=g)).cuda().requires_grad_(True)
+    o1 = exposure_affine(img, M, off)
+    img2, M2, off2 = (t.detach().clone().requires_grad_(True) for t in (img, M, off))
+    o2 = (img2.permute(1, 2, 0).reshape(-1, 3) @ M2.T + off2).view(H, W, 3).permute(2, 0, 1)
+    torch.testing.assert_close(o1, o2, rtol=1e-5, atol=1e-6)
+    (o1 * w).sum().backward()
+    (o2 * w).sum().backward()
+    torch.testing.assert_close(img.grad, img2.grad, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(M.grad, M2.grad, rtol=1e-4, atol=1e-3)
+    torch.testing.assert_close(off.grad, off2.grad, rtol=1e-4, atol=1e-3)

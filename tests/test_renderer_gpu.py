@@ -215,7 +215,10 @@ def test_render_postprocessing_matches_reference_golden(case, monkeypatch):
     for k in ("render", "surf_depth", "rend_alpha", "rend_normal", "surf_normal", "contributions"):
         key = p + "res." + k
         if key in z.files:
-            torch.testing.assert_close(res[k].detach().cpu(), torch.from_numpy(z[key]), rtol=1e-5, atol=1e-6)
+            # surf_normal: a normalised sum of cross products of neighbour differences (fp32 evaluation order differs
+            # from torch's: the kernel is pinned tighter against an eager restatement in tests/test_losses_gpu.py)
+            tol = dict(rtol=1e-3, atol=2e-5) if k == "surf_normal" else dict(rtol=1e-5, atol=1e-6)
+            torch.testing.assert_close(res[k].detach().cpu(), torch.from_numpy(z[key]), **tol)
     for k in ("visibility_filter", "radii"):
         assert np.array_equal(res[k].cpu().numpy(), z[p + "res." + k])
     # backward of the post-processing: gradient of the fixed loss w.r.t. the rasterizer outputs
