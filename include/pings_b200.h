@@ -176,6 +176,9 @@ int64_t pg_raster_band_records(int width, int height, int64_t num_rendered, void
 typedef struct PgNeuralMap {
   int64_t buffer_size;              /* config.buffer_size (NP:52) */
   const int64_t* buffer_pt_index;   /* [buffer_size] int64 slot table, -1 = empty (NP:86-88) */
+  const int32_t* buffer_pt_index32; /* optional int32 mirror of the slot table (pg_np_build_slot_mirror): when non-NULL
+                                       the kernels probe it instead (4-B slots, half the footprint: 400 MB at the
+                                       default buffer_size 1e8); the caller rebuilds it whenever the table changes */
   const float* neural_points;       /* [n_points,3] */
   int64_t n_points;
   const int64_t* neighbor_dx;       /* [K,3] cell offsets (NP:1026-1059) */
@@ -188,6 +191,9 @@ typedef struct PgNeuralMap {
   int32_t cur_ts;
   float diff_travel_dist_local;
 } PgNeuralMap;
+
+/* int32 copy of the int64 slot table (indices fit: n_points < 2^31). */
+int pg_np_build_slot_mirror(int64_t buffer_size, const int64_t* table64, int32_t* table32, void* stream);
 
 /* radius_neighborhood_search: dist2 [N,K] f32 and idx [N,K] i64 exactly as NP:1061-1115 returns them. */
 int pg_np_radius_search(const PgNeuralMap* map, int64_t N, const float* query_xyz, int time_filtering,

@@ -55,7 +55,8 @@ PG_MLP_MAX_LAYERS = 6
 
 
 class PgNeuralMap(C.Structure):
-    _fields_ = [("buffer_size", C.c_int64), ("buffer_pt_index", fp), ("neural_points", fp), ("n_points", C.c_int64),
+    _fields_ = [("buffer_size", C.c_int64), ("buffer_pt_index", fp), ("buffer_pt_index32", fp), ("neural_points", fp),
+                ("n_points", C.c_int64),
                 ("neighbor_dx", fp), ("K", C.c_int32), ("primes", C.c_int64 * 3), ("resolution", C.c_float),
                 ("max_valid_dist2", C.c_float), ("point_ts_create", fp), ("travel_dist", fp), ("cur_ts", C.c_int32),
                 ("diff_travel_dist_local", C.c_float)]
@@ -148,6 +149,8 @@ def lib() -> C.CDLL:
                                               C.c_float, C.c_int, fp, fp, fp, fp, fp]
     L.pg_photo_depth_loss_backward.restype = C.c_int
     L.pg_photo_depth_loss_backward.argtypes = [C.c_int, C.c_int, C.c_float, fp, fp, fp, fp, fp, fp, fp]
+    L.pg_np_build_slot_mirror.restype = C.c_int
+    L.pg_np_build_slot_mirror.argtypes = [C.c_int64, fp, fp, fp]
     L.pg_np_radius_search.restype = C.c_int
     L.pg_np_radius_search.argtypes = [C.POINTER(PgNeuralMap), C.c_int64, fp, C.c_int, fp, fp, fp]
     L.pg_np_query_feature.restype = C.c_int

@@ -42,7 +42,7 @@ using namespace pg;
 
 extern "C" {
 
-int pg_abi_version(void) { return 2; }
+int pg_abi_version(void) { return 3; }
 const char* pg_last_error(void) { return g_last_error; }
 
 int pg_timing_enable(int on) {

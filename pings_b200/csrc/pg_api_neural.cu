@@ -1,4 +1,5 @@
 // C-ABI entry points of the neural-point path (see include/pings_b200.h).
+#include <cstdlib>
 #include "pg_sdf.cuh"
 #include "pg_mlp_tc.cuh"
 
@@ -22,6 +23,7 @@ NpMapDev to_dev(const PgNeuralMap* m, int time_filtering) {
     d.bs_magic = bs ? ~0ull / bs : 0ull;
   }
   d.table = reinterpret_cast<const long long*>(m->buffer_pt_index);
+  d.table32 = m->buffer_pt_index32;
   d.pts = m->neural_points;
   d.n_points = m->n_points;
   d.dx = reinterpret_cast<const long long*>(m->neighbor_dx);
@@ -92,7 +94,20 @@ int with_cpl(int K, F&& f) {
 
 }  // namespace
 
+__global__ void __launch_bounds__(256) np_slot_mirror_kernel(long long n, const long long* __restrict__ t64,
+                                                             int* __restrict__ t32) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) t32[i] = (int)t64[i];
+}
+
 extern "C" {
+
+int pg_np_build_slot_mirror(int64_t buffer_size, const int64_t* table64, int32_t* table32, void* stream) {
+  if (buffer_size <= 0 || !table64 || !table32) return PG_ERR_ARG;
+  cudaStream_t st = (cudaStream_t)stream;
+  np_slot_mirror_kernel<<<kSmCount * 16, 256, 0, st>>>(buffer_size, reinterpret_cast<const long long*>(table64), table32);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
 
 int pg_np_radius_search(const PgNeuralMap* map, int64_t N, const float* q, int time_filtering, float* out_dist2,
                         int64_t* out_idx, void* stream) {
@@ -229,6 +244,29 @@ int pg_sdf_query(const PgNeuralMap* map, const PgQueryArgs* args, const PgMlp* m
   const MlpDev md = to_dev(mlp);
   const size_t smem = sdf_smem_floats(md) * sizeof(float);
   if (smem > kMaxDynSmem) return PG_ERR_UNSUPPORTED;
+  // batched kernel (lane-per-query MLP) for two-layer decoders and batches that fill the device; PG_SDF_IMPL=warp
+  // forces the warp-per-query kernel (dev A/B knob)
+  static const int force_warp = [] { const char* e = getenv("PG_SDF_IMPL"); return (e && e[0] == 'w') ? 1 : 0; }();
+  const size_t smem_b = sdf_batch_smem_floats(md, args->nn_k) * sizeof(float);
+  if (!force_warp && sdf_batch_supported(md) && N >= 4096 && smem_b <= kMaxDynSmem) {
+    const long long nbatch = (N + 31) / 32;
+    long long blocks = (nbatch + kSdfWarps - 1) / kSdfWarps;
+    const long long cap = (long long)kSmCount * 4;
+    if (blocks > cap) blocks = cap;
+    Phase ph("sdf_query", st);
+    return with_cpl(map->K, [&](auto cpl) {
+      auto launch = [&](auto kern) {
+        PG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_b));
+        kern<<<(unsigned)blocks, kSdfWarps * 32, smem_b, st>>>(m, a, md, sdf_scale, N, q, sdf,
+                                                               args->weighted_first ? nullptr : sdf_std,
+                                                               reinterpret_cast<long long*>(nn_counts));
+        PG_LAUNCH_CHECK(0, st);
+        return PG_OK;
+      };
+      if (md.hidden == 64) return launch(sdf_query_batch_kernel<decltype(cpl)::value, 64>);
+      return launch(sdf_query_batch_kernel<decltype(cpl)::value, 32>);
+    });
+  }
   long long blocks = (N + kSdfWarps - 1) / kSdfWarps;
   const long long cap = (long long)kSmCount * 8;  // persistent CTAs: weights are staged once per CTA
   if (blocks > cap) blocks = cap;

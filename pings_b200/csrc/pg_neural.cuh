@@ -25,6 +25,7 @@ struct NpMapDev {
   long long buffer_size;
   unsigned long long bs_magic;   // floor(2^64 / buffer_size): exact remainder without the 64-bit division routine
   const long long* table;
+  const int* table32;            // optional int32 mirror of `table` (same slots; half the footprint), or NULL
   const float* pts;
   long long n_points;
   const long long* dx;
@@ -53,19 +54,22 @@ __device__ __forceinline__ long long np_hash_base(const NpMapDev& m, long long g
                      (unsigned long long)gz * (unsigned long long)m.p2);
 }
 
-// `h` = un-reduced hash of the probed cell.
-__device__ __forceinline__ void np_probe_h(const NpMapDev& m, long long h, float qx, float qy, float qz,
-                                           long long& idx, float& dist2) {
-  // h % buffer_size with the sign of the dividend (torch.remainder on int64 as used at NP:1078-1084 is
-  // the C remainder), then the negative-index wrap (NP:1084).  Barrett: q = hi64(|h| * floor(2^64/d))
-  // is at most 1 below the true quotient, so r = |h| - q*d < 2d.
+// h mod buffer_size in [0, buffer_size): torch.fmod on int64 (NP:1078-1084) is the C remainder, and the negative
+// results then wrap as Python indices (NP:1084) - together the floored modulo.  Barrett: q = hi64(|h| *
+// floor(2^64/d)) is at most 1 below the true quotient, so r = |h| - q*d < 2d.
+__device__ __forceinline__ long long np_slot_of(const NpMapDev& m, long long h) {
   const unsigned long long d = (unsigned long long)m.buffer_size;
   const unsigned long long ah = h < 0 ? 0ull - (unsigned long long)h : (unsigned long long)h;
   unsigned long long r = ah - __umul64hi(ah, m.bs_magic) * d;
   if (r >= d) r -= d;
   if (r >= d) r -= d;
-  const long long hv = (h < 0 && r != 0) ? (long long)(d - r) : (long long)r;
-  idx = m.table[hv];
+  return (h < 0 && r != 0) ? (long long)(d - r) : (long long)r;
+}
+
+// Probe of slot `hv` of the table.
+__device__ __forceinline__ void np_probe_slot(const NpMapDev& m, long long hv, float qx, float qy, float qz,
+                                              long long& idx, float& dist2) {
+  idx = m.table32 ? (long long)m.table32[hv] : m.table[hv];
   if (m.time_filtering) {
     const int ts = m.ts_create[np_wrap(idx, m.n_points)];
     const float diff = fabsf(m.travel[m.cur_ts] - m.travel[ts]);
@@ -78,6 +82,12 @@ __device__ __forceinline__ void np_probe_h(const NpMapDev& m, long long h, float
   dist2 = __fadd_rn(__fadd_rn(__fmul_rn(sx, sx), __fmul_rn(sy, sy)), __fmul_rn(sz, sz));
   if (idx == -1) dist2 = m.max_valid;
   if (dist2 > m.max_valid) idx = -1;
+}
+
+// `h` = un-reduced hash of the probed cell.
+__device__ __forceinline__ void np_probe_h(const NpMapDev& m, long long h, float qx, float qy, float qz,
+                                           long long& idx, float& dist2) {
+  np_probe_slot(m, np_slot_of(m, h), qx, qy, qz, idx, dist2);
 }
 
 __device__ __forceinline__ long long np_cell(float q, float res) { return (long long)floorf(__fdiv_rn(q, res)); }
@@ -124,16 +134,27 @@ constexpr int kNpMaxK = 32;             // nn_k <= 32 (one kept neighbour per la
 // Runs the probes of one query on the calling warp and leaves the nn_k nearest valid neighbours in
 // lanes [0, nn_k): (sel_d, sel_i) with sel_i the FINAL (local) index or -1. Returns nn_count.
 // Per-lane hash deltas of the probes c*32 + lane (query independent: hoist out of persistent loops).
+// dr = the same deltas reduced to [0, buffer_size): (h0 + dh) mod d == (h0 mod d + dh mod d) mod d as long as the
+// int64 sum does not wrap, so a query pays ONE 64-bit Barrett reduction (its base cell) and every probe a 32-bit
+// add + conditional subtract instead of ~30 instructions of 64-bit arithmetic (buffer_size < 2^31).
 template <int CPL>
-__device__ __forceinline__ void np_lane_deltas(const NpMapDev& m, int lane, long long (&dh)[CPL]) {
+__device__ __forceinline__ void np_lane_deltas(const NpMapDev& m, int lane, long long (&dh)[CPL], uint32_t (&dr)[CPL]) {
 #pragma unroll
-  for (int c = 0; c < CPL; ++c) dh[c] = (c * 32 + lane < m.K) ? np_hash_delta(m, c * 32 + lane) : 0;
+  for (int c = 0; c < CPL; ++c) {
+    dh[c] = (c * 32 + lane < m.K) ? np_hash_delta(m, c * 32 + lane) : 0;
+    dr[c] = (uint32_t)np_slot_of(m, dh[c]);
+  }
 }
 
 template <int CPL>
-__device__ __forceinline__ int np_warp_knn(const NpMapDev& m, const NpQueryDev& a, const long long (&dh)[CPL], float qx,
-                                           float qy, float qz, int lane, float& sel_d, int& sel_i) {
+__device__ __forceinline__ int np_warp_knn(const NpMapDev& m, const NpQueryDev& a, const long long (&dh)[CPL],
+                                           const uint32_t (&dr)[CPL], float qx, float qy, float qz, int lane, float& sel_d,
+                                           int& sel_i) {
   const long long h0 = np_hash_base(m, np_cell(qx, m.res), np_cell(qy, m.res), np_cell(qz, m.res));
+  // fast path: no int64 wrap possible in h0 + dh (|h0| < 2^62, |dh| < 2^40) and 32-bit slots
+  const bool fast = m.buffer_size < (1ll << 31) && h0 > -(1ll << 62) && h0 < (1ll << 62);
+  const uint32_t b0 = fast ? (uint32_t)np_slot_of(m, h0) : 0u;
+  const uint32_t d32 = (uint32_t)m.buffer_size;
   float cd[CPL];
   int ci[CPL];
   int cnt = 0;
@@ -145,7 +166,13 @@ __device__ __forceinline__ int np_warp_knn(const NpMapDev& m, const NpQueryDev& 
     if (k < m.K) {
       long long idx;
       float d;
-      np_probe_h(m, (long long)((unsigned long long)h0 + (unsigned long long)dh[c]), qx, qy, qz, idx, d);
+      if (fast) {
+        uint32_t slot = b0 + dr[c];
+        if (slot >= d32) slot -= d32;
+        np_probe_slot(m, (long long)slot, qx, qy, qz, idx, d);
+      } else {
+        np_probe_h(m, (long long)((unsigned long long)h0 + (unsigned long long)dh[c]), qx, qy, qz, idx, d);
+      }
       if (idx >= 0) {
         if (a.use_only_measured && a.free_mask[idx]) idx = -1;
         if (idx >= 0 && a.use_only_valid && !a.valid_mask[idx]) idx = -1;
@@ -292,8 +319,9 @@ __global__ void __launch_bounds__(kNpWarps * 32) np_query_kernel(NpMapDev m, NpQ
   float sel_d;
   int sel_i;
   long long dh[CPL];
-  np_lane_deltas<CPL>(m, lane, dh);
-  const int cnt = np_warp_knn<CPL>(m, a, dh, qx, qy, qz, lane, sel_d, sel_i);
+  uint32_t dr[CPL];
+  np_lane_deltas<CPL>(m, lane, dh, dr);
+  const int cnt = np_warp_knn<CPL>(m, a, dh, dr, qx, qy, qz, lane, sel_d, sel_i);
   const float w = np_idw_weight(sel_d, sel_i, a.nn_k, cnt, lane);
   if (lane < a.nn_k) {
     weight[n * a.nn_k + lane] = w;

@@ -183,11 +183,29 @@ class NeuralPoints(nn.Module):
         self.max_valid_dist2 = 3 * ((num_nei_cells + 1) * self.resolution) ** 2
 
     # ------------------------------------------------------------------ C-ABI plumbing
+    def _slot_mirror(self):
+        """int32 mirror of the int64 slot table (the reference layout, NP:86-88, is kept as the source of truth so a
+        live reference map can be shared): 4-byte probes, half the footprint (400 MB at buffer_size 1e8).  Rebuilt
+        when the table tensor was replaced or modified in place (torch's version counter); `use_slot_mirror = False`
+        turns it off."""
+        if not getattr(self, "use_slot_mirror", True) or not self.buffer_pt_index.is_cuda:
+            return None
+        key = (self.buffer_pt_index.data_ptr(), self.buffer_pt_index._version, int(self.buffer_size))
+        cache = getattr(self, "_mirror_cache", None)
+        if cache is None or cache[0] != key:
+            t32 = torch.empty(int(self.buffer_size), dtype=torch.int32, device=self.buffer_pt_index.device)
+            with torch.cuda.device(t32.device):
+                L.check(L.lib().pg_np_build_slot_mirror(int(self.buffer_size), self.buffer_pt_index.data_ptr(), t32.data_ptr(),
+                                                        torch.cuda.current_stream(t32.device).cuda_stream), "slot mirror")
+            self._mirror_cache = cache = (key, t32)
+        return cache[1].data_ptr()
+
     def _map_struct(self, time_filtering: bool):
         m = L.PgNeuralMap()
         self._keep = [self.buffer_pt_index, self.neural_points, self.neighbor_dx]
         m.buffer_size = int(self.buffer_size)
         m.buffer_pt_index = self.buffer_pt_index.data_ptr()
+        m.buffer_pt_index32 = self._slot_mirror()
         m.neural_points = self.neural_points.data_ptr()
         m.n_points = self.neural_points.shape[0]
         m.neighbor_dx = self.neighbor_dx.data_ptr()
