@@ -619,12 +619,51 @@ def sdf_leg(args, local, world=1, rank=0, keep=None) -> dict:
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms, e2e_ms, train_ms = [float(x) for x in t]
+    # map-sized variant: ~5e5 neural points, queries spread over the whole map (slot-table probes miss L2)
+    big = {}
+    try:
+        npm_b, dec_b, q_b = SN.large_map_and_queries(device=dev)
+        if rank > 0:
+            q_b = q_b[torch.randperm(q_b.shape[0], device=dev)]
+        for _ in range(warm):
+            npm_b.sdf_fused(q_b, dec_b)
+        torch.cuda.synchronize()
+        evb = []
+        for _ in range(steps):
+            flush.fill_(1)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            npm_b.sdf_fused(q_b, dec_b)
+            b.record()
+            evb.append((a, b))
+        torch.cuda.synchronize()
+        ms_b = sum(a.elapsed_time(b) for a, b in evb) / steps
+        tb = torch.tensor([ms_b], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tb, op=dist.ReduceOp.MAX)
+        ms_b = float(tb.item())
+        Nb = q_b.shape[0]
+        # per query: 81 probes x one 32-B sector each (what the hardware moves for a 4-B slot) + neighbour rows + output
+        sect = Nb * (81 * 32 + 332 + 12)
+        big = {"value": round(world * Nb / (ms_b * 1e-3), 1), "unit": "queries/s", "ms_per_step": round(ms_b, 4),
+               "neural_points": int(npm_b.count()), "queries_per_step_per_gpu": Nb,
+               "roofline": {"bound": "hbm", "alg_bytes_per_query": 600 + 332 + 12,
+                            "achieved": round(Nb * (600 + 332 + 12) / (ms_b * 1e-3) / 1e9, 1),
+                            "sector_bytes_per_query": 81 * 32 + 332 + 12,
+                            "sector_gbs": round(sect / (ms_b * 1e-3) / 1e9, 1), "peak": peaks()["hbm_gbs"],
+                            "frac": round(Nb * (600 + 332 + 12) / (ms_b * 1e-3) / 1e9 / peaks()["hbm_gbs"], 4),
+                            "frac_sectors": round(sect / (ms_b * 1e-3) / 1e9 / peaks()["hbm_gbs"], 4)}}
+        del npm_b
+    except Exception as ex:   # noqa: BLE001
+        big = f"failed: {ex!r}"
     pk = peaks()
-    alg = N * (600 + 332 + 4 + 8)  # kNN 600 B + gather/IDW 332 B (int64 slot table kept: +0), + outputs
+    alg = N * (600 + 332 + 4 + 8)  # kNN 600 B + gather/IDW 332 B (int32 slot mirror), + outputs
     gbs = alg / (ms * 1e-3) / 1e9
     return {"sdf": {"metric": "SDF queries/s (fused kNN+IDW+decoder, C1)", "value": round(world * N / (ms * 1e-3), 1),
                     "unit": "queries/s", "ms_per_step": round(ms, 4), "queries_per_step_per_gpu": N,
-                    "neural_points": int(npm.count()), "slot_table": "int64[1e8] (800 MB, reference layout)",
+                    "neural_points": int(npm.count()),
+                    "slot_table": "int32 mirror [1e8] (400 MB) of the reference's int64 table",
+                    "large_map": big,
                     "e2e": {"value": round(world * N / (e2e_ms * 1e-3), 1), "unit": "queries/s",
                             "h2d_bytes_per_step": N * 12, "d2h_bytes_per_step": N * 4},
                     "train_fwd_bwd_bs10000": {"value": round(world * 10000 / (train_ms * 1e-3), 1), "unit": "queries/s",

@@ -64,3 +64,31 @@ def oracle_state(npm: NeuralPoints) -> dict:
     S.update(resolution=float(npm.resolution), buffer_size=int(npm.buffer_size), max_valid_dist2=npm.max_valid_dist2,
              cur_ts=int(npm.cur_ts), diff_travel_dist_local=float(npm.diff_travel_dist_local))
     return S
+
+
+def large_map_and_queries(device="cuda", seed: int = 7, nx: int = 1000, ny: int = 500, n_queries: int = 115_200,
+                          buffer_size: int = int(1e8)):
+    """A map-sized variant of C1: ~5e5 neural points - one per 0.4 m voxel of a 400 m x 200 m
+    ground sheet with gentle relief, as a multi-frame trajectory would leave it - inserted through update(), PIN-SLAM
+    settings otherwise, and scan-sized query batches drawn uniformly over the sheet, so that the 81 slot-table probes of
+    a query land in DRAM (at C1's 7,033 points the touched slots sit in L2)."""
+    g = torch.Generator().manual_seed(seed)
+    cfg = default_config(device=device, buffer_size=buffer_size, track_on=False, temporal_local_map_off=True,
+                         local_map_radius=1e4, sorrounding_map_radius=1.4e4)
+    res = cfg.voxel_size_m
+    ix, iy = torch.meshgrid(torch.arange(nx, dtype=torch.float32), torch.arange(ny, dtype=torch.float32), indexing="ij")
+    x = (ix.reshape(-1) + 0.5) * res - nx * res / 2
+    y = (iy.reshape(-1) + 0.5) * res - ny * res / 2
+    z = 0.15 * torch.sin(x / 7.0) * torch.cos(y / 9.0) - 1.73
+    pts = torch.stack([x, y, z], 1) + (torch.rand(nx * ny, 3, generator=g) - 0.5) * torch.tensor([0.3, 0.3, 0.02])
+    npm = NeuralPoints(cfg)
+    npm.travel_dist = torch.zeros(1, device=device)
+    npm.update(pts.to(device), None, None, torch.zeros(3, device=device), None, 0)
+    n = npm.count()
+    npm.geo_features = (0.1 * torch.randn(n + 1, cfg.feature_dim, generator=g)).to(device)
+    npm.reset_local_map(torch.zeros(3, device=device), None, 0)
+    torch.manual_seed(seed)
+    dec = Decoder(cfg, cfg.feature_dim, 64, 1, 1)
+    sel = torch.randint(0, pts.shape[0], (n_queries,), generator=g)
+    q = (pts[sel] + 0.05 * torch.randn(n_queries, 3, generator=g)).contiguous().to(device)
+    return npm, dec, q
