@@ -379,6 +379,17 @@ int pg_ssim_backward(int B, int C, int H, int W, float C1, float C2, const float
                      const float* dL_dmap, float dL_dmap_scalar, const float* dm_dmu1, const float* dm_dsigma1_sq,
                      const float* dm_dsigma12, float* dL_dimg1, void* stream);
 
+/* fused_ssim(img1, img2, padding="same") as the caller uses it (FS/fused_ssim/__init__.py:34-42: `map.mean()`): the
+ * mean of the SSIM map is reduced inside the forward (sum_scratch: one double of device scratch), the map itself is
+ * never written, and the backward takes the upstream gradient of the mean as a device scalar.  dm_* may be NULL
+ * (no backward wanted). */
+int pg_ssim_mean_forward(int B, int C, int H, int W, float C1, float C2, const float* img1, const float* img2,
+                         float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12, double* sum_scratch, float* mean,
+                         void* stream);
+int pg_ssim_mean_backward(int B, int C, int H, int W, const float* img1, const float* img2, const float* upstream,
+                          const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12, float* dL_dimg1,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -173,6 +173,10 @@ def lib() -> C.CDLL:
     L.pg_ssim_forward.argtypes = [C.c_int] * 4 + [C.c_float] * 2 + [fp] * 7
     L.pg_ssim_backward.restype = C.c_int
     L.pg_ssim_backward.argtypes = [C.c_int] * 4 + [C.c_float] * 2 + [fp, fp, fp, C.c_float, fp, fp, fp, fp, fp]
+    L.pg_ssim_mean_forward.restype = C.c_int
+    L.pg_ssim_mean_forward.argtypes = [C.c_int] * 4 + [C.c_float] * 2 + [fp] * 8
+    L.pg_ssim_mean_backward.restype = C.c_int
+    L.pg_ssim_mean_backward.argtypes = [C.c_int] * 4 + [fp] * 8
     L.pg_depth2normal_forward.restype = C.c_int
     L.pg_depth2normal_forward.argtypes = [C.c_int, C.c_int] + [C.c_float] * 4 + [fp] * 5
     L.pg_depth2normal_backward.restype = C.c_int

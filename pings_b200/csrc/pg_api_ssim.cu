@@ -17,7 +17,8 @@ int pg_ssim_forward(int B, int C, int H, int W, float C1, float C2, const float*
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(div_up(W, kSsTile), div_up(H, kSsTile), B * C);
   Phase ph("ssim_fwd", st);
-  ssim_fwd_kernel<<<grid, kSsThreads, 0, st>>>(H, W, C1, C2, img1, img2, ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12);
+  ssim_fwd_kernel<<<grid, kSsThreads, 0, st>>>(H, W, C1, C2, img1, img2, ssim_map, dm_dmu1, dm_dsigma1_sq, dm_dsigma12,
+                                              nullptr);
   PG_LAUNCH_CHECK(0, st);
   return PG_OK;
 }
@@ -33,8 +34,45 @@ int pg_ssim_backward(int B, int C, int H, int W, float C1, float C2, const float
   cudaStream_t st = (cudaStream_t)stream;
   dim3 grid(div_up(W, kSsTile), div_up(H, kSsTile), B * C);
   Phase ph("ssim_bwd", st);
-  ssim_bwd_kernel<<<grid, kSsThreads, 0, st>>>(H, W, img1, img2, dL_dmap, dL_dmap_scalar, dm_dmu1, dm_dsigma1_sq,
-                                              dm_dsigma12, dL_dimg1);
+  ssim_bwd_kernel<<<grid, kSsThreads, 0, st>>>(H, W, img1, img2, dL_dmap, dL_dmap_scalar, nullptr, dm_dmu1,
+                                              dm_dsigma1_sq, dm_dsigma12, dL_dimg1);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+__global__ void ssim_mean_finish_kernel(const double* __restrict__ sum, double count, float* __restrict__ mean) {
+  mean[0] = (float)(sum[0] / count);
+}
+
+int pg_ssim_mean_forward(int B, int C, int H, int W, float C1, float C2, const float* img1, const float* img2,
+                         float* dm_dmu1, float* dm_dsigma1_sq, float* dm_dsigma12, double* sum_scratch, float* mean,
+                         void* stream) {
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0 || !img1 || !img2 || !sum_scratch || !mean) return PG_ERR_ARG;
+  const bool train = dm_dmu1 != nullptr;
+  if (train && (!dm_dsigma1_sq || !dm_dsigma12)) return PG_ERR_ARG;
+  if ((long long)B * C > 65535) return PG_ERR_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  PG_CUDA(cudaMemsetAsync(sum_scratch, 0, sizeof(double), st));
+  dim3 grid(div_up(W, kSsTile), div_up(H, kSsTile), B * C);
+  Phase ph("ssim_fwd", st);
+  ssim_fwd_kernel<<<grid, kSsThreads, 0, st>>>(H, W, C1, C2, img1, img2, nullptr, dm_dmu1, dm_dsigma1_sq, dm_dsigma12,
+                                              sum_scratch);
+  ssim_mean_finish_kernel<<<1, 1, 0, st>>>(sum_scratch, (double)B * C * H * W, mean);
+  PG_LAUNCH_CHECK(0, st);
+  return PG_OK;
+}
+
+int pg_ssim_mean_backward(int B, int C, int H, int W, const float* img1, const float* img2, const float* upstream,
+                          const float* dm_dmu1, const float* dm_dsigma1_sq, const float* dm_dsigma12, float* dL_dimg1,
+                          void* stream) {
+  if (B <= 0 || C <= 0 || H <= 0 || W <= 0) return PG_ERR_ARG;
+  if (!img1 || !img2 || !upstream || !dm_dmu1 || !dm_dsigma1_sq || !dm_dsigma12 || !dL_dimg1) return PG_ERR_ARG;
+  if ((long long)B * C > 65535) return PG_ERR_UNSUPPORTED;
+  cudaStream_t st = (cudaStream_t)stream;
+  dim3 grid(div_up(W, kSsTile), div_up(H, kSsTile), B * C);
+  Phase ph("ssim_bwd", st);
+  ssim_bwd_kernel<<<grid, kSsThreads, 0, st>>>(H, W, img1, img2, nullptr, (float)(1.0 / ((double)B * C * H * W)), upstream,
+                                              dm_dmu1, dm_dsigma1_sq, dm_dsigma12, dL_dimg1);
   PG_LAUNCH_CHECK(0, st);
   return PG_OK;
 }
