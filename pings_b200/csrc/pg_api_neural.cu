@@ -244,11 +244,12 @@ int pg_sdf_query(const PgNeuralMap* map, const PgQueryArgs* args, const PgMlp* m
   const MlpDev md = to_dev(mlp);
   const size_t smem = sdf_smem_floats(md) * sizeof(float);
   if (smem > kMaxDynSmem) return PG_ERR_UNSUPPORTED;
-  // batched kernel (lane-per-query MLP) for two-layer decoders and batches that fill the device; PG_SDF_IMPL=warp
-  // forces the warp-per-query kernel (dev A/B knob)
-  static const int force_warp = [] { const char* e = getenv("PG_SDF_IMPL"); return (e && e[0] == 'w') ? 1 : 0; }();
+  // Measured on B200 (C1, 115,200 queries): warp-per-query 0.227 ms, batched 0.256 ms - the batched kernel's 16
+  // resident warps per SM (128 registers) hide the probe latency worse than its cheaper decoder saves, so the
+  // warp-per-query kernel stays the default; PG_SDF_IMPL=batch selects the batched one (dev A/B knob).
+  static const int use_batch = [] { const char* e = getenv("PG_SDF_IMPL"); return (e && e[0] == 'b') ? 1 : 0; }();
   const size_t smem_b = sdf_batch_smem_floats(md, args->nn_k) * sizeof(float);
-  if (!force_warp && sdf_batch_supported(md) && N >= 4096 && smem_b <= kMaxDynSmem) {
+  if (use_batch && sdf_batch_supported(md) && N >= 4096 && smem_b <= kMaxDynSmem) {
     const long long nbatch = (N + 31) / 32;
     long long blocks = (nbatch + kSdfWarps - 1) / kSdfWarps;
     const long long cap = (long long)kSmCount * 4;
