@@ -29,7 +29,7 @@ def staged_only() -> bool:
 def _stub():
     for m in ["open3d", "matplotlib", "matplotlib.cm", "matplotlib.pyplot", "roma", "imageio", "wandb", "natsort",
               "open3d.visualization", "open3d.visualization.gui", "open3d.visualization.rendering", "pypose", "kornia",
-              "cv2", "plyfile", "rich", "gtsam", "pytorch3d", "skimage", "skimage.metrics", "lpips"]:
+              "cv2", "plyfile", "rich", "gtsam", "pytorch3d", "skimage", "skimage.metrics", "skimage.measure", "lpips"]:
         if m not in sys.modules:
             try:
                 __import__(m)
