@@ -208,10 +208,31 @@ def roofline_tables(phase_ms: dict, ab: dict, pk: dict, l2: dict | None = None):
 
 
 # Issue-slot view of the blend kernels (they are not HBM-bound: DRAM < 1 % in ncu): warp instructions executed per
-# launch from the committed ncu --set full capture (profiles/, smsp__inst_executed.sum) over the kernel's duration,
-# against the B200 peak of 148 SMs x 4 schedulers x 1 warp-instruction / clock at the 1.965 GHz maximum SM clock.
-ISSUE_PEAK_GINST = 148 * 4 * 1.965
-ISSUE_ROOFLINE: dict = {}
+# launch on the C2 scene from the committed ncu --set full capture (profiles/r02_ncu_full_c2.csv,
+# smsp__inst_executed.sum; a property of the scene, not of the clock) over the kernel's LIVE duration, against the
+# B200 issue peak of 148 SMs x 4 schedulers x 1 warp-instruction / clock at the SM clock sampled during the run.
+ISSUE_INST: dict = {"render_fwd": 76315285, "render_bwd": 92457944, "preprocess_fwd": 8637648,
+                    "preprocess_bwd": 14840160, "depth_sort": 6114119}
+
+
+def issue_roofline(phase_ms: dict, sm_mhz: float, pairs: int) -> dict:
+    """Per kernel: G warp-instructions/s achieved vs the issue peak; for the blend kernels also pixel-Gaussian
+    pairs/s (pairs = sum over pixels of the list position of the last contributor, i.e. what the walk visits) and
+    thread-instructions per pair."""
+    peak = 148 * 4 * (sm_mhz or 1965.0) * 1e-3
+    out = {"peak_ginst_s": round(peak, 1), "source": "profiles/r02_ncu_full_c2.csv (smsp__inst_executed.sum), live durations"}
+    for k, inst in ISSUE_INST.items():
+        ms = phase_ms.get(k, 0.0)
+        if ms <= 0:
+            continue
+        g = inst / (ms * 1e-3) / 1e9
+        row = {"warp_inst_per_launch": inst, "ginst_s": round(g, 1), "frac": round(g / peak, 4)}
+        if k.startswith("render_") and pairs > 0:
+            row["pairs_per_launch"] = int(pairs)
+            row["gpairs_s"] = round(pairs / (ms * 1e-3) / 1e9, 2)
+            row["thread_inst_per_pair"] = round(inst * 32 / pairs, 1)
+        out[k] = row
+    return out
 
 
 def launches_per_step(T: int, P: int) -> int:
@@ -262,7 +283,7 @@ def run_ours(args, rank, world, local):
                                               sc["rotations"], 1.0, e, view, full, proj, cam.tanfovx, cam.tanfovy,
                                               ct["color"], ct["depth"], e, 0, center, geom, R, binning, img, False,
                                               param_grads_out=flat)
-        last_binning[:] = [binning]
+        last_binning[:] = [binning, geom, img]
         if world > 1 and exchange:
             # training exchange step: sum the Gaussian-parameter gradients over the view shards (the backward wrote
             # them straight into the flat buffer).  The all-reduce runs on a side stream and overlaps the next
@@ -442,6 +463,11 @@ def run_ours(args, rank, world, local):
     ab = algorithmic_bytes(P, R, W, H, Q)
     pk = peaks()
     per_kernel, per_phase, dom = roofline_tables(phase_ms, ab, pk, l2_bytes(P, R))
+    pairs = 0
+    if last_binning:
+        dv = RC.debug_views(0, P, W, H, int(R), last_binning[1], last_binning[0], last_binning[2])
+        pairs = int(dv["n_contrib"].to(torch.int64).sum().item())
+    issue = issue_roofline(phase_ms, float(clocks.get("sm_mhz") or 0.0), pairs) if P == C2["P"] else {}
     achieved = per_kernel[dom]["gbs"]
     T = ((W + 15) // 16) * ((H + 15) // 16)
     line = {
@@ -466,7 +492,7 @@ def run_ours(args, rank, world, local):
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": pk["hbm_gbs"],
                      "unit": "GB/s", "frac": round(achieved / pk["hbm_gbs"], 4), "traffic": TRAFFIC.get(dom),
                      "peak_source": pk["source"], "kernels": per_kernel, "phases": per_phase,
-                     "issue": ISSUE_ROOFLINE,
+                     "issue": issue,
                      "note": "kernel = the single longest kernel of the step (per-kernel CUDA-event pairs on the launching "
                              "stream, separate pass); `phases` folds the six band-binning kernels into `binning`; the "
                              "blend kernels are issue-bound (see `issue`), HBM fractions are reported for all"},
@@ -474,12 +500,13 @@ def run_ours(args, rank, world, local):
     return line
 
 
-# per-launch dram bytes of the dominant kernels from profiles/ (ncu --set full), filled in as captured
-# (profiles/r01_ncu_full_c2_v7.csv: dram__bytes_read.sum + dram__bytes_write.sum, summed over the
-# kernels of a phase; the capture runs the step without the L2 flush, so inputs produced by the previous
-# kernel are L2 hits)
-TRAFFIC: dict = {"preprocess_fwd": 29.0e6, "depth_sort": 6.05e6, "binning": 82.5e6, "render_fwd": 3.41e6,
-                 "render_bwd": 13.05e6, "preprocess_bwd": 51.7e6, "sdf_query": 12.7e6}
+# per-launch dram bytes (dram__bytes_read.sum + dram__bytes_write.sum) from the committed ncu --set full capture of
+# the C2 step (profiles/r02_ncu_full_c2.csv) and of the C1 SDF query (profiles/r02_ncu_full_sdf.csv); the capture
+# runs the step without the L2 flush, so inputs produced by the previous kernel are L2 hits
+TRAFFIC: dict = {"preprocess_fwd": 28.7e6, "depth_sort": 6.11e6, "band_rows_kernel<count>": 3.42e6,
+                 "band_list_scan_kernel": 1.19e6, "band_rows_kernel<write>": 6.31e6, "band_expand_kernel<count>": 15.1e6,
+                 "band_tile_scan_kernel": 2.80e6, "band_expand_kernel<write>": 51.4e6, "render_fwd": 3.53e6,
+                 "render_bwd": 13.05e6, "preprocess_bwd": 50.5e6, "sdf_query": 11.9e6}
 
 
 def cpu_baseline_line(args) -> dict | None:

@@ -20,7 +20,7 @@ cap() {  # name, kernel regex, skip, count, command...
 }
 # C2 step: skip the warm-up steps' launches, capture one full step of library kernels
 cap c2 "^(r3_|band_|depth_sort)" 33 11 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --legs none
-cap c3 "^(rs_render|rs_pre|r3_preprocess_bwd|ssim_|depth_sort|band_)" 26 13 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --legs surfel
+cap c3 "^(rs_render|rs_pre|ssim_)" 10 5 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --legs surfel
 cap c4 "^(spawn_|mlp_|np_|depth2normal|exposure|photo_)" 60 24 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --legs mapping
 cap sdf "^(sdf_query)" 12 2 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --legs sdf
 rm -f $out/*.ncu-rep
