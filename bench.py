@@ -239,7 +239,10 @@ def launches_per_step(T: int, P: int) -> int:
     """Kernel launches of one fwd+bwd (radix pass = hist + 3 scan + scatter)."""
     scan = 3
     rp = 1 + scan + 1
-    if (P + 4095) // 4096 <= 296:        # one cooperative launch: 4 LSD passes + rect gather + weight scan
+    band = BAND_LISTS.get("n", 1 << 30) <= 1024
+    if band and os.environ.get("PG_SORT_IMPL", "b")[0] != "r":
+        pre = 1 + 4                      # preprocess + bucket sort: histogram, scan, scatter, local sort
+    elif (P + 4095) // 4096 <= 296:      # one cooperative launch: 4 LSD passes + rect gather + weight scan
         pre = 1 + 1
     else:
         pre = 1 + 4 * rp + 1 + scan      # preprocess, depth argsort, rect gather, weight scan

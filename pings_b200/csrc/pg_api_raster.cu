@@ -85,7 +85,7 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
   if (rc != PG_OK) return rc;
   GeomWs ws;
   carve_geom(prm->variant, P, geom_ws, &ws);
-  PG_CUDA(cudaMemsetAsync(ws.total, 0, sizeof(unsigned long long), st));
+  PG_CUDA(cudaMemsetAsync(ws.total, 0, 2 * sizeof(unsigned long long), st));
   R3PreArgs a;
   a.P = P; a.D = prm->sh_degree; a.M = prm->sh_coeffs; a.W = W; a.H = H; a.gx = gx; a.gy = gy;
   a.means = g->means3D; a.scales = g->scales; a.rots = g->rotations; a.opac = g->opacities; a.shs = g->shs;

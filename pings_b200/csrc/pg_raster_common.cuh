@@ -17,7 +17,9 @@
 //      sorted on the tile bits only (1-2 passes over R items of 6 bytes)
 #pragma once
 #include "pg_common.cuh"
+#include <cstdlib>
 #include "pg_sort.cuh"
+#include "pg_bucket_sort.cuh"
 #include "pg_bin_band.cuh"
 
 namespace pg {
@@ -30,6 +32,32 @@ constexpr uint32_t kBigRect = 24;  // rects with >= this many tiles are walked c
 __host__ __device__ __forceinline__ uint32_t bin_weight(uint32_t tiles) {
   if (tiles == 0) return 0u;
   return tiles < kBigRect ? 8u * tiles + 16u : tiles + 32u;
+}
+
+// Tail of the two preprocess kernels: block-reduced instance count and the key range of the visible Gaussians
+// (max(key), max(~key) so that a zero fill initialises both) for the bucket sort; 3 atomics per CTA.
+// total[0] = instances (u64), total[1] viewed as u32[2] = {max key, max ~key}.
+__device__ __forceinline__ void preprocess_block_tail(uint32_t my_tiles, uint32_t key, unsigned long long* total) {
+  __shared__ uint32_t red[3][8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const bool valid = my_tiles != 0;
+  uint32_t s = __reduce_add_sync(0xffffffffu, my_tiles);
+  uint32_t hi = __reduce_max_sync(0xffffffffu, valid ? key : 0u);
+  uint32_t lo = __reduce_max_sync(0xffffffffu, valid ? ~key : 0u);
+  if (lane == 0) { red[0][warp] = s; red[1][warp] = hi; red[2][warp] = lo; }
+  __syncthreads();
+  if (warp == 0) {
+    const int nw = (int)(blockDim.x >> 5);
+    s = __reduce_add_sync(0xffffffffu, lane < nw ? red[0][lane] : 0u);
+    hi = __reduce_max_sync(0xffffffffu, lane < nw ? red[1][lane] : 0u);
+    lo = __reduce_max_sync(0xffffffffu, lane < nw ? red[2][lane] : 0u);
+    if (lane == 0 && s) {
+      atomicAdd(total, (unsigned long long)s);
+      uint32_t* mm = reinterpret_cast<uint32_t*>(total + 1);
+      atomicMax(mm, hi);
+      atomicMax(mm + 1, lo);
+    }
+  }
 }
 
 struct GeomWs {
@@ -50,7 +78,7 @@ struct GeomWs {
   uint32_t* offsets;      // [P] exclusive scan of tiles in depth order
   uint8_t* clamped;       // [3P] SH clamp flags
   uint32_t* sort_scratch; // radix/scan scratch for P items
-  unsigned long long* total;  // [1] number of instances
+  unsigned long long* total;  // [2] number of instances; [1] = {max key, max ~key} of the visible Gaussians (u32 x 2)
   double* tau_acc;        // [8] pose-gradient accumulators (6 used) + block counter
   float4* gacc;           // [3P] (3DGS) / [4P] (surfel) backward gradient accumulation records
   size_t gacc_count;      // number of float4 in gacc
@@ -76,7 +104,10 @@ inline size_t carve_geom(int variant, int P, void* base, GeomWs* ws) {
   w.sorted_idx = c.take<uint32_t>(p);
   w.offsets = c.take<uint32_t>(p);
   w.clamped = c.take<uint8_t>(3 * p);
-  w.sort_scratch = c.take<uint32_t>(depth_sort_scratch_elems(p));
+  {
+    const size_t s1 = depth_sort_scratch_elems(p), s2 = bucket_sort_scratch_elems(p);
+    w.sort_scratch = c.take<uint32_t>(s1 > s2 ? s1 : s2);
+  }
   w.total = c.take<unsigned long long>(2);
   w.tau_acc = c.take<double>(8);
   w.gacc_count = (variant == PG_VARIANT_SURFEL ? 4 : 3) * p;
@@ -401,11 +432,22 @@ __global__ void __launch_bounds__(256) gather_rect_kernel(int P, const uint32_t*
 // Depth argsort + offsets (stage 1 tail).  Leaves Gaussian ids in ws.sorted_idx.
 // `offsets` = exclusive scan in depth order of the binning weights (counting path; total -> ws.wtotal)
 // or of the tile counts (radix path).
+// PG_SORT_IMPL=radix keeps the 4-pass LSD radix sort on the band path (A/B measurements, parity tests of both).
+inline bool sort_force_radix() {
+  const char* e = getenv("PG_SORT_IMPL");
+  return e && e[0] == 'r';
+}
+
 inline cudaError_t depth_order_and_offsets(const GeomWs& ws, int P, bool fast, cudaStream_t st, bool need_offsets = true) {
   cudaError_t e;
   const uint32_t n = (uint32_t)P;
   const uint32_t nblk = sort_num_blocks(n);
   const bool compact = !need_offsets;   // band path: only the visible Gaussians are sorted (count in ws.nvalid)
+  if (compact && !sort_force_radix()) {
+    // keyA | keyB | valA are carved back to back (128-B padding): >= 8 bytes per Gaussian for the (key, id) pairs
+    return depth_bucket_sort(ws.dkey, reinterpret_cast<const uint32_t*>(ws.total + 1), ws.sort_scratch,
+                             reinterpret_cast<unsigned long long*>(ws.keyA), ws.rect, ws.sorted_idx, ws.srect, ws.nvalid, n, st);
+  }
   if (depth_sort_coop_fits(nblk)) {
     DepthSortArgs a;
     a.dkey = ws.dkey; a.keyA = ws.keyA; a.valA = ws.valA; a.keyB = ws.keyB; a.valB = ws.sorted_idx;

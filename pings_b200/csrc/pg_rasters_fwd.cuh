@@ -133,7 +133,7 @@ __global__ void __launch_bounds__(256) rs_preprocess_kernel(RSPreArgs a, int* __
                                                             uint2* __restrict__ rect, uint8_t* __restrict__ clamped,
                                                             unsigned long long* __restrict__ total) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t my_tiles = 0;
+  uint32_t my_tiles = 0, my_key = 0xffffffffu;
   if (idx < a.P) {
     int radius = 0;
     uint32_t key = 0xffffffffu;
@@ -216,12 +216,10 @@ __global__ void __launch_bounds__(256) rs_preprocess_kernel(RSPreArgs a, int* __
     tiles[idx] = my_tiles;
     wts[idx] = bin_weight(my_tiles);
     dkey[idx] = key;
+    my_key = key;
     if (!my_tiles) rect[idx] = make_uint2(0u, 0u);
   }
-  uint32_t s = my_tiles;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  if ((threadIdx.x & 31) == 0 && s) atomicAdd(total, (unsigned long long)s);
+  preprocess_block_tail(my_tiles, my_key, total);
 }
 
 // checkFrustum of the surfel rasterizer (RS rasterizer_impl.cu:54-66 / auxiliary.h:177-208).

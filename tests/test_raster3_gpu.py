@@ -299,3 +299,49 @@ def test_binning_lists_bitexact_edge_cases(P, W, H, seed, scale_mul):
     assert torch.equal(dv["ranges"], r["ranges"])
     assert torch.equal(dv["n_contrib"], r["n_contrib"])
     torch.testing.assert_close(color, r["color"], rtol=IMG_RTOL, atol=IMG_ATOL)
+
+
+# Depth-order edge cases for the bucket sort (pg_bucket_sort.cuh): bins that hold hundreds to thousands of Gaussians
+# within a few depth-bit values of each other (CTA-wide shared-memory and in-place global bitonic paths), one
+# outlier stretching the key range, and the LSD radix path kept behind PG_SORT_IMPL=radix.
+@pytest.mark.gpu
+@pytest.mark.parametrize("P,clusters,impl", [
+    (6000, 1, "bucket"),       # every visible Gaussian at (nearly) one depth: one bin, global-memory path
+    (9000, 8, "bucket"),       # eight depth clusters of ~1100: shared-memory CTA path
+    (40000, 300, "bucket"),    # ~130 per cluster + outlier: warp networks of every size
+    (40000, 0, "bucket"),
+    (40000, 0, "radix"),
+])
+def test_depth_order_bitexact_degenerate_depths(P, clusters, impl, monkeypatch):
+    from oracle.ref_api import RefRaster3, available
+    from pings_b200 import _raster_c as RC
+    if not available("ref_r3"):
+        pytest.fail("oracle/_ref/libref_r3.so missing: run __graft_entry__.build() where /root/reference exists")
+    if impl == "radix":
+        monkeypatch.setenv("PG_SORT_IMPL", "radix")
+    else:
+        monkeypatch.delenv("PG_SORT_IMPL", raising=False)
+    W, H = 320, 200
+    cam, sc, mats, ct = _scene(P, W, H, 21 + clusters)
+    view, full, proj, center = mats
+    if clusters:
+        m = sc["means3D"]
+        pv = torch.cat([m, torch.ones_like(m[:, :1])], 1) @ view          # camera frame (row vectors)
+        z = pv[:, 2]
+        lo, hi = float(z.min()), float(z.max())
+        q = torch.round((z - lo) / max(hi - lo, 1e-6) * (clusters - 1)) if clusters > 1 else torch.zeros_like(z)
+        znew = lo + 0.5 * (hi - lo) + (q - 0.5 * (clusters - 1)) * (hi - lo) / max(clusters, 1)
+        pv = torch.stack([pv[:, 0] * znew / z, pv[:, 1] * znew / z, znew, pv[:, 3]], 1)   # same pixel, new depth
+        sc["means3D"] = (pv @ torch.linalg.inv(view))[:, :3].contiguous()
+        if clusters == 300:
+            sc["means3D"][0] = sc["means3D"][0] + (sc["means3D"][0] - center) * 2000.0    # far outlier on the same ray
+    bg = torch.zeros(3, device="cuda")
+    R, color, radii, geom, binning, img, depth, opac, n_touched = _mine_forward(cam, sc, mats, W, H, bg, debug=True)
+    ref = RefRaster3()
+    r = ref.forward(sc, (view, full, proj), W, H, cam.tanfovx, cam.tanfovy, bg, campos=center)
+    assert R == r["num_rendered"] and R > 0
+    dv = RC.debug_views(0, P, W, H, R, geom, binning, img)
+    assert torch.equal(radii, r["radii"])
+    assert torch.equal(dv["point_list"], r["point_list"])
+    assert torch.equal(dv["ranges"], r["ranges"])
+    assert torch.equal(dv["n_contrib"], r["n_contrib"])
