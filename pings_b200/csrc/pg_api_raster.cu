@@ -85,7 +85,7 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
   if (rc != PG_OK) return rc;
   GeomWs ws;
   carve_geom(prm->variant, P, geom_ws, &ws);
-  PG_CUDA(cudaMemsetAsync(ws.total, 0, 2 * sizeof(unsigned long long), st));
+  PG_CUDA(cudaMemsetAsync(ws.total, 0, geom_zero_bytes(P, band_path(gx, gy) && !sort_force_radix()), st));
   R3PreArgs a;
   a.P = P; a.D = prm->sh_degree; a.M = prm->sh_coeffs; a.W = W; a.H = H; a.gx = gx; a.gy = gy;
   a.means = g->means3D; a.scales = g->scales; a.rots = g->rotations; a.opac = g->opacities; a.shs = g->shs;
@@ -157,15 +157,16 @@ int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, vo
   PG_LAUNCH_CHECK(prm->debug, st);
   {
     Phase ph("render_fwd", st);
+    // launched as the programmatic dependent of the last binning kernel (a plain launch when there was none)
     if (surfel)
-      rs_render_fwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, gw.ext, gw.zyv,
-                                                          prm->bg, prm->config, out->out_color, out->out_normal,
-                                                          out->out_depth, out->out_opacity, iw.final_T, iw.final_D,
-                                                          iw.n_contrib, out->contributions);
+      PG_CUDA(launch_pdl(rs_render_fwd_kernel, (unsigned)(gx * gy), (unsigned)kRThreads, 0, st, (const uint2*)iw.ranges,
+                         point_list, W, H, gx, (const float4*)gw.rec, (const float4*)gw.ext, (const float*)gw.zyv,
+                         (const float*)prm->bg, (const float*)prm->config, out->out_color, out->out_normal,
+                         out->out_depth, out->out_opacity, iw.final_T, iw.final_D, iw.n_contrib, out->contributions));
     else
-      r3_render_fwd_kernel<<<gx * gy, kRThreads, 0, st>>>(iw.ranges, point_list, W, H, gx, gw.rec, prm->bg,
-                                                          out->out_color, out->out_depth, out->out_opacity,
-                                                          iw.final_T, iw.n_contrib, out->n_touched);
+      PG_CUDA(launch_pdl(r3_render_fwd_kernel, (unsigned)(gx * gy), (unsigned)kRThreads, 0, st, (const uint2*)iw.ranges,
+                         point_list, W, H, gx, (const float4*)gw.rec, (const float*)prm->bg, out->out_color,
+                         out->out_depth, out->out_opacity, iw.final_T, iw.n_contrib, out->n_touched));
   }
   PG_LAUNCH_CHECK(prm->debug, st);
   return PG_OK;

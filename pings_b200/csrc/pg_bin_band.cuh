@@ -64,7 +64,11 @@ template <bool WRITE>
 __global__ void __launch_bounds__(kBandWarps * 32) band_rows_kernel(
     int P, const uint32_t* __restrict__ nvalid, int NB, int GY, int nchunks, const uint32_t* __restrict__ sorted_idx,
     const uint2* __restrict__ srect, uint32_t* __restrict__ matA, const uint32_t* __restrict__ lstart,
-    uint32_t* __restrict__ recs) {
+    uint32_t* __restrict__ recs, uint32_t* __restrict__ tickets) {
+  pdl_trigger();
+  pdl_wait();
+  // the count pass is the head of the chain: it also clears the two last-block tickets of the scan kernels
+  if (!WRITE && blockIdx.x == 0 && threadIdx.x < 2) tickets[threadIdx.x] = 0u;
   // the depth sort dropped the culled Gaussians: V = *nvalid items, cut into nchunks equal chunks of whole 32-groups
   P = min(P, (int)*nvalid);
   const int per_warp = ((P + nchunks - 1) / nchunks + 31) & ~31;
@@ -141,6 +145,8 @@ __device__ __forceinline__ bool band_last_block(uint32_t* ticket) {
 __global__ void __launch_bounds__(256) band_list_scan_kernel(int nL, int nchunks, uint32_t* __restrict__ matA,
                                                              uint32_t* __restrict__ lcount, uint32_t* __restrict__ lstart,
                                                              uint32_t* __restrict__ segbase, uint32_t* __restrict__ ticket) {
+  pdl_trigger();
+  pdl_wait();
   {
     // CTA = list blockIdx.x; thread t owns entries [16 t, 16 t + 16) of the row (nchunks <= 4096, multiple of 8)
     uint32_t* row = matA + (size_t)blockIdx.x * nchunks;
@@ -238,6 +244,8 @@ __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
     const uint32_t* __restrict__ tiletot, const uint32_t* __restrict__ tilestart, uint32_t* __restrict__ out) {
   extern __shared__ uint32_t band_sm[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  pdl_trigger();
+  pdl_wait();
   uint32_t* sb = band_sm;                                      // [nL + 1]
   const int sb_words = (nL + 1 + 31) & ~31;
   // WRITE only: per warp [cap] staged words, [32] run deltas
@@ -320,6 +328,8 @@ __global__ void __launch_bounds__(256) band_tile_scan_kernel(int nL, int NB, int
                                                              uint32_t* __restrict__ ticket) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slots = nL * kBandTiles;
+  pdl_trigger();
+  pdl_wait();
   for (int slot = blockIdx.x * 8 + warp; slot < slots; slot += gridDim.x * 8) {
     const int l = slot / kBandTiles, x = slot % kBandTiles;
     const uint32_t sb = segbase[l], nseg = segbase[l + 1] - sb;
@@ -382,40 +392,48 @@ inline cudaError_t band_bin(const BandWs& w, int P, const uint32_t* nvalid, int 
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (sms <= 0) sms = 148;
   }
-  cudaError_t e = cudaMemsetAsync(w.ticket, 0, 2 * sizeof(uint32_t), st);
-  if (e != cudaSuccess) return e;
   const int ctasA = nchunks / kBandWarps;
-  // one timed phase per kernel (opt-in phase timer): bench.py reports the roofline of a single kernel
+  const unsigned thr = kBandWarps * 32;
+  const uint32_t* cnull = nullptr;
+  uint32_t* null = nullptr;
+  cudaError_t e;
+  // one timed phase per kernel (opt-in phase timer): bench.py reports the roofline of a single kernel.  The six
+  // kernels are a programmatic-dependent-launch chain (pg_common.cuh); the head is a plain launch.
   {
     Phase ph("band_rows_kernel<count>", st);
-    band_rows_kernel<false><<<ctasA, kBandWarps * 32, smA, st>>>(P, nvalid, NB, gy, nchunks, sorted_idx, srect, w.matA,
-                                                                 nullptr, nullptr);
+    band_rows_kernel<false><<<ctasA, thr, smA, st>>>(P, nvalid, NB, gy, nchunks, sorted_idx, srect, w.matA, cnull, null, w.ticket);
   }
   {
     Phase ph("band_list_scan_kernel", st);
-    band_list_scan_kernel<<<nL, 256, 0, st>>>(nL, nchunks, w.matA, w.lcount, w.lstart, w.segbase, w.ticket);
+    e = launch_pdl(band_list_scan_kernel, (unsigned)nL, 256u, 0, st, nL, nchunks, w.matA, w.lcount, w.lstart, w.segbase, w.ticket);
+    if (e != cudaSuccess) return e;
   }
   {
     Phase ph("band_rows_kernel<write>", st);
-    band_rows_kernel<true><<<ctasA, kBandWarps * 32, smA, st>>>(P, nvalid, NB, gy, nchunks, sorted_idx, srect, w.matA,
-                                                                w.lstart, w.recs);
+    e = launch_pdl(band_rows_kernel<true>, (unsigned)ctasA, thr, smA, st, P, nvalid, NB, gy, nchunks, sorted_idx, srect,
+                   w.matA, (const uint32_t*)w.lstart, w.recs, w.ticket);
+    if (e != cudaSuccess) return e;
   }
   {
     Phase ph("band_expand_kernel<count>", st);
-    band_expand_kernel<false><<<sms * 8, kBandWarps * 32, smC, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect, w.tilemat,
-                                                                      nullptr, nullptr, nullptr);
+    e = launch_pdl(band_expand_kernel<false>, (unsigned)(sms * 8), thr, smC, st, nL, NB, (const uint32_t*)w.lstart,
+                   (const uint32_t*)w.segbase, (const uint32_t*)w.recs, rect, w.tilemat, cnull, cnull, null);
+    if (e != cudaSuccess) return e;
   }
   const int slots = nL * kBandTiles;
   const int ctasT = (slots + 7) / 8 < sms * 8 ? (slots + 7) / 8 : sms * 8;
   {
     Phase ph("band_tile_scan_kernel", st);
-    band_tile_scan_kernel<<<ctasT, 256, 0, st>>>(nL, NB, gx, T, w.segbase, w.tilemat, w.tiletot, w.tilestart, ranges,
-                                                 w.ticket + 1);
+    e = launch_pdl(band_tile_scan_kernel, (unsigned)ctasT, 256u, 0, st, nL, NB, gx, T, (const uint32_t*)w.segbase, w.tilemat,
+                   w.tiletot, w.tilestart, ranges, w.ticket + 1);
+    if (e != cudaSuccess) return e;
   }
   {
     Phase ph("band_expand_kernel<write>", st);
-    band_expand_kernel<true><<<sms * 3, kBandWarps * 32, smW, st>>>(nL, NB, w.lstart, w.segbase, w.recs, rect, w.tilemat,
-                                                                     w.tiletot, w.tilestart, out);
+    e = launch_pdl(band_expand_kernel<true>, (unsigned)(sms * 3), thr, smW, st, nL, NB, (const uint32_t*)w.lstart,
+                   (const uint32_t*)w.segbase, (const uint32_t*)w.recs, rect, w.tilemat, (const uint32_t*)w.tiletot,
+                   (const uint32_t*)w.tilestart, out);
+    if (e != cudaSuccess) return e;
   }
   (void)R;
   return cudaGetLastError();

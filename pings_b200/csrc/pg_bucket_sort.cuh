@@ -37,6 +37,12 @@ inline size_t bucket_sort_scratch_elems(uint64_t n) {
   return nb + 2 * (nb / 4096) + 16 + bucket_max_buckets(n) + 4;
 }
 
+// words at the head of the scratch that must be zero before the histogram: bins | look-back words | misc
+inline size_t bucket_sort_zero_words(uint64_t n) {
+  const size_t nb = (size_t)1 << bucket_log_bins(n);
+  return nb + 2 * (nb / 4096) + 16;
+}
+
 struct BucketSortArgs {
   const uint32_t* dkey;        // [n] depth bits, 0xFFFFFFFF = culled
   const uint32_t* mm;          // [2] max(key), max(~key) over the valid keys (0, 0 when there is none)
@@ -62,6 +68,7 @@ __device__ __forceinline__ void bucket_map(const uint32_t* __restrict__ mm, int 
 }
 
 __global__ void __launch_bounds__(256) bucket_hist_kernel(const BucketSortArgs a) {
+  pdl_trigger();
   uint32_t kmin; int shift;
   bucket_map(a.mm, a.lognb, kmin, shift);
   const uint32_t t = blockIdx.x * 256 + threadIdx.x;
@@ -86,6 +93,8 @@ __global__ void __launch_bounds__(256) bucket_scan_kernel(const BucketSortArgs a
   __shared__ uint32_t s_prefix;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t base = blockIdx.x * 4096u + threadIdx.x * 16u;
+  pdl_trigger();
+  pdl_wait();
   uint32_t c[16];
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
@@ -148,6 +157,8 @@ __global__ void __launch_bounds__(256) bucket_scan_kernel(const BucketSortArgs a
 }
 
 __global__ void __launch_bounds__(256) bucket_scatter_kernel(const BucketSortArgs a) {
+  pdl_trigger();
+  pdl_wait();
   uint32_t kmin; int shift;
   bucket_map(a.mm, a.lognb, kmin, shift);
   const uint32_t t = blockIdx.x * 256 + threadIdx.x;
@@ -294,6 +305,7 @@ __device__ __forceinline__ void cta_bitonic(unsigned long long* d, uint32_t n) {
 __global__ void __launch_bounds__(32) bucket_local_sort_kernel(const BucketSortArgs a) {
   const int lane = threadIdx.x;
   const uint32_t b = blockIdx.x;
+  pdl_wait();
   if (b >= a.misc[0]) return;
   const uint32_t s = a.bstart[b], n = a.bstart[b + 1] - s;
   if (n == 0) return;
@@ -312,7 +324,8 @@ __global__ void __launch_bounds__(32) bucket_local_sort_kernel(const BucketSortA
   }
 }
 
-// Host side: one memset + four launches on `st`.  `scratch` holds bucket_sort_scratch_elems(n) words.
+// Host side: four launches on `st`.  `scratch` holds bucket_sort_scratch_elems(n) words, of which the first
+// bucket_sort_zero_words(n) were zeroed by the caller (before the kernel that writes `mm`).
 inline cudaError_t depth_bucket_sort(const uint32_t* dkey, const uint32_t* mm, uint32_t* scratch, unsigned long long* pairs,
                                      const uint2* rect, uint32_t* sorted_idx, uint2* srect, uint32_t* nvalid, uint32_t n,
                                      cudaStream_t st) {
@@ -324,13 +337,14 @@ inline cudaError_t depth_bucket_sort(const uint32_t* dkey, const uint32_t* mm, u
   a.misc = scratch + nb + 2 * nscan;
   a.bstart = a.misc + 16;
   a.pairs = pairs; a.rect = rect; a.sorted_idx = sorted_idx; a.srect = srect; a.nvalid = nvalid;
-  cudaError_t e = cudaMemsetAsync(scratch, 0, (nb + 2 * nscan + 16) * sizeof(uint32_t), st);
-  if (e != cudaSuccess) return e;
   const uint32_t g4 = (uint32_t)(((size_t)n + 256 * kBucketKeys - 1) / (256 * kBucketKeys));
   bucket_hist_kernel<<<g4, 256, 0, st>>>(a);
-  bucket_scan_kernel<<<(uint32_t)nscan, 256, 0, st>>>(a);
-  bucket_scatter_kernel<<<g4, 256, 0, st>>>(a);
-  bucket_local_sort_kernel<<<(uint32_t)bucket_max_buckets(n), 32, 0, st>>>(a);
+  cudaError_t e = launch_pdl(bucket_scan_kernel, (unsigned)nscan, 256u, 0, st, a);
+  if (e != cudaSuccess) return e;
+  e = launch_pdl(bucket_scatter_kernel, g4, 256u, 0, st, a);
+  if (e != cudaSuccess) return e;
+  e = launch_pdl(bucket_local_sort_kernel, (unsigned)bucket_max_buckets(n), 32u, 0, st, a);
+  if (e != cudaSuccess) return e;
   return cudaGetLastError();
 }
 

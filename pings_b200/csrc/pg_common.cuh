@@ -1,5 +1,6 @@
 // Shared helpers for the pings_b200 CUDA sources (sm_100a only).
 #pragma once
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -65,6 +66,34 @@ struct Carver {
   }
   size_t total() const { return align_up(off, 128) + 128; }
 };
+
+// Programmatic dependent launch (sm_90+): kernels of a chain are launched with
+// programmaticStreamSerialization, so their CTAs are set up while the previous kernel drains; `pdl_wait` blocks until
+// the previous grid has completed and its writes are visible, and must precede every dependent access.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+// Every kernel of a chain calls pdl_wait() as its FIRST statement in every thread (a grid whose CTAs all left
+// without waiting would let its own dependent start before the grid two steps back has finished).
+template <typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(Args...), unsigned grid, unsigned block, size_t smem, cudaStream_t st,
+                              Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(block);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  // Opt-in (PG_PDL=1).  Measured on B200, C2 step, alternating runs on one box (tools/gpu_ab_pdl.sh): the depth-sort
+  // phase alone gets shorter (46 -> 40 us) but the whole step gets LONGER (0.529 -> 0.543 ms): the early-launched
+  // CTAs sit on the SMs' CTA slots / shared memory while the previous kernel still runs.  Plain launches by default.
+  static const bool on = [] { const char* e = getenv("PG_PDL"); return e && e[0] == '1'; }();
+  cfg.numAttrs = on ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
 
 __host__ __device__ inline int div_up(int a, int b) { return (a + b - 1) / b; }
 

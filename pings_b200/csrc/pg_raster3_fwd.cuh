@@ -209,6 +209,7 @@ __global__ void __launch_bounds__(kRThreads) r3_render_fwd_kernel(
     uint32_t* __restrict__ n_contrib, int* __restrict__ n_touched) {
   __shared__ RSlab sm;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  pdl_wait();   // tail of the binning chain (programmatic dependent launch)
   const int tile = blockIdx.x;
   const int tx = tile % gx, ty = tile / gx;
   // warp region and this lane's quad

@@ -104,11 +104,13 @@ inline size_t carve_geom(int variant, int P, void* base, GeomWs* ws) {
   w.sorted_idx = c.take<uint32_t>(p);
   w.offsets = c.take<uint32_t>(p);
   w.clamped = c.take<uint8_t>(3 * p);
+  // `total` (one 128-B line) sits immediately before the sort scratch: on the band path ONE memset clears the
+  // instance count, the key range and the bucket sort's bins / look-back words before the preprocess kernel
+  w.total = c.take<unsigned long long>(16);
   {
     const size_t s1 = depth_sort_scratch_elems(p), s2 = bucket_sort_scratch_elems(p);
     w.sort_scratch = c.take<uint32_t>(s1 > s2 ? s1 : s2);
   }
-  w.total = c.take<unsigned long long>(2);
   w.tau_acc = c.take<double>(8);
   w.gacc_count = (variant == PG_VARIANT_SURFEL ? 4 : 3) * p;
   w.gacc = c.take<float4>(w.gacc_count);
@@ -432,6 +434,11 @@ __global__ void __launch_bounds__(256) gather_rect_kernel(int P, const uint32_t*
 // Depth argsort + offsets (stage 1 tail).  Leaves Gaussian ids in ws.sorted_idx.
 // `offsets` = exclusive scan in depth order of the binning weights (counting path; total -> ws.wtotal)
 // or of the tile counts (radix path).
+// Bytes to clear at ws.total before the preprocess kernel (`bucket`: the depth order will use the bucket sort).
+inline size_t geom_zero_bytes(int P, bool bucket) {
+  return bucket ? 128 + bucket_sort_zero_words((uint64_t)(P > 0 ? P : 1)) * sizeof(uint32_t) : 2 * sizeof(unsigned long long);
+}
+
 // PG_SORT_IMPL=radix keeps the 4-pass LSD radix sort on the band path (A/B measurements, parity tests of both).
 inline bool sort_force_radix() {
   const char* e = getenv("PG_SORT_IMPL");
@@ -445,6 +452,7 @@ inline cudaError_t depth_order_and_offsets(const GeomWs& ws, int P, bool fast, c
   const bool compact = !need_offsets;   // band path: only the visible Gaussians are sorted (count in ws.nvalid)
   if (compact && !sort_force_radix()) {
     // keyA | keyB | valA are carved back to back (128-B padding): >= 8 bytes per Gaussian for the (key, id) pairs
+    // (bins and look-back words were zeroed together with ws.total before the preprocess kernel: geom_zero_bytes)
     return depth_bucket_sort(ws.dkey, reinterpret_cast<const uint32_t*>(ws.total + 1), ws.sort_scratch,
                              reinterpret_cast<unsigned long long*>(ws.keyA), ws.rect, ws.sorted_idx, ws.srect, ws.nvalid, n, st);
   }
@@ -481,11 +489,13 @@ inline cudaError_t bin_instances(const GeomWs& g, const BinWs& b, const ImageWs&
                                  int64_t R, const uint32_t** point_list, cudaStream_t st) {
   const int gx = div_up(W, kTile), gy = div_up(H, kTile);
   const int T = gx * gy;
-  cudaError_t e = cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * (size_t)T, st);
-  if (e != cudaSuccess) return e;
+  cudaError_t e = cudaSuccess;
   *point_list = b.valA;
+  // the band binning writes the range of every tile itself
+  if (R > 0 && P > 0 && band_path(gx, gy)) return band_bin(b.band, P, g.nvalid, gx, gy, R, g.sorted_idx, g.srect, g.rect, b.valA, im.ranges, st);
+  e = cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * (size_t)T, st);
+  if (e != cudaSuccess) return e;
   if (R <= 0 || P <= 0) return cudaSuccess;
-  if (band_path(gx, gy)) return band_bin(b.band, P, g.nvalid, gx, gy, R, g.sorted_idx, g.srect, g.rect, b.valA, im.ranges, st);
   if (bin_fast_path(T)) {
     const int nchunks = bin_max_chunks(T);
     const int wpc = bin_warps_per_cta(T);

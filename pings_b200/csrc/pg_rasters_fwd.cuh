@@ -273,6 +273,7 @@ __global__ void __launch_bounds__(kRThreads) rs_render_fwd_kernel(
     float* __restrict__ contributions) {
   __shared__ RSSlab sm;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  pdl_wait();   // tail of the binning chain (programmatic dependent launch)
   const int tile = blockIdx.x;
   const int tx = tile % gx, ty = tile / gx;
   const int rx0 = tx * kTile, ry0 = ty * kTile + warp * 8;
