@@ -336,6 +336,22 @@ size_t pg_spawn_count_index(int64_t NK);
 int pg_spawn_epilogue_forward(const PgSpawnArgs* args, const PgSpawnOut* out, void* stream);
 int pg_spawn_epilogue_backward(const PgSpawnArgs* args, const PgSpawnGrads* grads, void* stream);
 
+/* Allocation-free variant of pg_spawn_epilogue_forward.  It has NO counterpart in the reference: it was added
+ * for callers that cannot allocate device memory (CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  The look-back scratch (`out->state`, ignored here and may be NULL) lives
+ * in a file-scope `static __device__` array inside the library: 256 KiB per GPU that loads the library, held until
+ * the process exits, enough for n*K <= PG_SPAWN_STATIC_MAX_NK candidate Gaussians; larger calls return
+ * PG_ERR_UNSUPPORTED with the limit in pg_last_error().  The call does no cudaMalloc / cudaFree and calls no
+ * allocating library routine: one cudaMemsetAsync of the scratch words it uses, the kernel, and one 8-byte
+ * device-to-device copy on `stream`.  count_nan_out: device pointer to 2 words = {number of kept Gaussians, 1 if a
+ * rotation is NaN} (what the allocating entry point leaves at state[pg_spawn_count_index(n*K)]).  All other inputs and
+ * outputs are the caller's, exactly as for pg_spawn_epilogue_forward, and the results are identical.
+ * Every call on a device shares the one array and the array keeps the last call's contents (the call clears what it
+ * needs): calls that OVERLAP on the same GPU (different streams, concurrent host threads) race - serialise them. */
+#define PG_SPAWN_STATIC_MAX_NK (1ll << 24)
+int pg_spawn_epilogue_forward_static(const PgSpawnArgs* args, const PgSpawnOut* out, uint32_t* count_nan_out,
+                                     void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Post-raster loss assembly (utils/mapper.py:1239,1252-1267): loss = mean|rgb - gt_rgb| +
  * lambda_depth * mean over valid pixels of |gt_depth - depth| (or |1/gt_depth - 1/depth| when

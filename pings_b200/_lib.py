@@ -195,6 +195,8 @@ def lib() -> C.CDLL:
     L.pg_spawn_count_index.argtypes = [C.c_int64]
     L.pg_spawn_epilogue_forward.restype = C.c_int
     L.pg_spawn_epilogue_forward.argtypes = [C.POINTER(PgSpawnArgs), C.POINTER(PgSpawnOut), fp]
+    L.pg_spawn_epilogue_forward_static.restype = C.c_int
+    L.pg_spawn_epilogue_forward_static.argtypes = [C.POINTER(PgSpawnArgs), C.POINTER(PgSpawnOut), fp, fp]
     L.pg_spawn_epilogue_backward.restype = C.c_int
     L.pg_spawn_epilogue_backward.argtypes = [C.POINTER(PgSpawnArgs), C.POINTER(PgSpawnGrads), fp]
     _declare_optional(L)
