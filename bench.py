@@ -339,7 +339,16 @@ def run_ours(args, rank, world, local):
     value = world * W * H / (ms_per_step * 1e-3) / 1e6
 
     # ---- e2e through the public API with host buffers ----
-    pinned = {k: v.contiguous().pin_memory() for k, v in sc_cpu.items()}
+    # the host copy of the Gaussian parameters is ONE flat pinned buffer with the five tensors as views (the layout
+    # pings_b200.parallel.FlatAdamW keeps), so a step's upload is a single 28 MB H2D copy
+    keys = list(sc_cpu)
+    sizes = [sc_cpu[k].numel() for k in keys]
+    pinned_flat = torch.empty(sum(sizes), dtype=torch.float32).pin_memory()
+    pinned, off = {}, 0
+    for k, n_ in zip(keys, sizes):
+        pinned[k] = pinned_flat[off:off + n_].view(sc_cpu[k].shape)
+        pinned[k].copy_(sc_cpu[k])
+        off += n_
     target = target_cpu.to(dev)
     target_depth = torch.rand(1, H, W, generator=torch.Generator().manual_seed(78)).mul_(60.0).add_(1.0).to(dev)
     from pings_b200.losses import photo_depth_loss
@@ -353,7 +362,14 @@ def run_ours(args, rank, world, local):
     # Double-buffered input staging: the H2D copy of step k+1 runs on a copy stream while step k computes
     # (every copy is inside the timed region; only the first one is exposed).
     copy_stream = torch.cuda.Stream(device=dev)
-    slots = [{k: torch.empty_like(v, device=dev) for k, v in pinned.items()} for _ in range(2)]
+    slots_flat = [torch.empty_like(pinned_flat, device=dev) for _ in range(2)]
+    slots = []
+    for s_ in range(2):
+        d_, off = {}, 0
+        for k, n_ in zip(keys, sizes):
+            d_[k] = slots_flat[s_][off:off + n_].view(sc_cpu[k].shape)
+            off += n_
+        slots.append(d_)
     ready = [torch.cuda.Event() for _ in range(2)]
     consumed = [torch.cuda.Event() for _ in range(2)]
 
@@ -361,8 +377,7 @@ def run_ours(args, rank, world, local):
         slot = i & 1
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(consumed[slot])
-            for k, v in pinned.items():
-                slots[slot][k].copy_(v, non_blocking=True)
+            slots_flat[slot].copy_(pinned_flat, non_blocking=True)
             ready[slot].record(copy_stream)
 
     def step_e2e(i: int, prefetch: bool, more: bool = True):
@@ -444,6 +459,12 @@ def run_ours(args, rank, world, local):
 
     e2e_serial_ms = run_e2e(False)
     e2e_ms_per_step = run_e2e(True)
+    if os.environ.get("PG_E2E_PROFILE") and rank == 0:   # dev only: where the pipelined step's host and device time go
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+            run_e2e(True)
+        print(prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=40, max_name_column_width=60), file=sys.stderr)
+        print(prof.key_averages().table(sort_by="self_cuda_time_total", row_limit=25, max_name_column_width=60), file=sys.stderr)
     e2e_value = world * W * H / (e2e_ms_per_step * 1e-3) / 1e6
     e2e_serial_value = world * W * H / (e2e_serial_ms * 1e-3) / 1e6
 

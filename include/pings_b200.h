@@ -113,6 +113,18 @@ int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g,
                              void* geom_ws, void* binning_ws, size_t binning_bytes,
                              void* image_ws, int64_t num_rendered,
                              const PgRasterFwdOut* out, void* stream);
+/* Stage 1 + stage 2 queued back to back, the host waits for the instance count only AFTER the last launch (the
+ * reference blocks between its preprocess and its sort, R3 rasterizer_impl.cu:283-284, because it sizes the binning
+ * buffer from the count).  The caller passes a binning workspace carved for `capacity` instances
+ * (pg_raster_binning_bytes(variant, W, H, capacity); e.g. the previous frame's count plus a margin); the kernels
+ * check the device-side count against it and leave without writing when it does not fit.
+ * Returns PG_OK with *num_rendered = R when R <= capacity (outputs complete; the backward / debug views take
+ * num_rendered = R with this same workspace), PG_ERR_WORKSPACE with *num_rendered = R when R > capacity (the caller
+ * allocates for R and calls pg_raster_forward_stage2 - stage 1's results in geom_ws stay valid), PG_ERR_UNSUPPORTED
+ * for tile grids off the band-binning path (use the two-stage calls). */
+int pg_raster_forward_optimistic(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, size_t geom_bytes,
+                                 int32_t* radii, void* binning_ws, size_t binning_bytes, int64_t capacity,
+                                 void* image_ws, const PgRasterFwdOut* out, int64_t* num_rendered, void* stream);
 
 typedef struct PgRasterBwdIn {
   const float* dL_dout_color;   /* [3,H,W] */

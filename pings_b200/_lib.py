@@ -8,6 +8,8 @@ from __future__ import annotations
 import ctypes as C
 import os
 
+import torch
+
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("PINGS_B200_LIB") or os.path.join(_HERE, "libpings_b200.so")   # env override: dev A/B of two builds
 
@@ -135,6 +137,10 @@ def lib() -> C.CDLL:
     L.pg_raster_forward_stage2.restype = C.c_int
     L.pg_raster_forward_stage2.argtypes = [C.POINTER(PgRasterParams), C.POINTER(PgGaussians), fp, fp, C.c_size_t,
                                            fp, C.c_int64, C.POINTER(PgRasterFwdOut), fp]
+    L.pg_raster_forward_optimistic.restype = C.c_int
+    L.pg_raster_forward_optimistic.argtypes = [C.POINTER(PgRasterParams), C.POINTER(PgGaussians), fp, C.c_size_t, fp, fp,
+                                               C.c_size_t, C.c_int64, fp, C.POINTER(PgRasterFwdOut),
+                                               C.POINTER(C.c_int64), fp]
     L.pg_raster_backward.restype = C.c_int
     L.pg_raster_backward.argtypes = [C.POINTER(PgRasterParams), C.POINTER(PgGaussians), fp, fp, fp, C.c_int64,
                                      C.POINTER(PgRasterBwdIn), C.POINTER(PgRasterBwdOut), fp]
@@ -234,6 +240,31 @@ def check(rc: int, what: str) -> None:
     if rc != PG_OK:
         msg = lib().pg_last_error().decode() if rc == 2 else ""
         raise RuntimeError(f"pings_b200: {what} failed: {_ERR.get(rc, rc)} {msg}")
+
+
+class _NoGuard:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *a):
+        return False
+
+
+_NO_GUARD = _NoGuard()
+
+
+def device_guard(dev):
+    """`torch.cuda.device(dev)` only when another device is current (the context manager costs ~10 us per call)."""
+    idx = dev.index
+    if idx is None or idx == torch.cuda.current_device():
+        return _NO_GUARD
+    return torch.cuda.device(dev)
+
+
+def raw_stream(dev) -> int:
+    """cudaStream_t of torch's current stream on `dev` as an int."""
+    idx = dev.index
+    return torch._C._cuda_getCurrentRawStream(torch.cuda.current_device() if idx is None else idx)
 
 
 def ptr(t) -> int | None:

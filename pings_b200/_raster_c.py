@@ -8,6 +8,7 @@ C-ABI library on torch's current stream under a device guard.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
@@ -15,6 +16,8 @@ from . import _lib as L
 
 
 def _f32c(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype is torch.float32 and t.is_contiguous():   # the common case: nothing to do, no new tensor object
+        return t
     if t.numel() == 0:
         return t
     if t.dtype != torch.float32:
@@ -22,8 +25,50 @@ def _f32c(t: torch.Tensor) -> torch.Tensor:
     return t.contiguous()
 
 
-def _stream(dev) -> int:
-    return torch.cuda.current_stream(dev).cuda_stream
+_stream = L.raw_stream
+_guard = L.device_guard
+
+# Instance-count history per (variant, W, H): (last count, Gaussians of that call).  The forward carves its binning
+# workspace for the predicted count (+ margin) and launches both stages before it waits for the true one
+# (pg_raster_forward_optimistic); a wrong guess costs one re-run of stage 2, never a wrong result.
+_R_HISTORY: dict = {}
+_OPTIMISTIC = os.environ.get("PG_RASTER_OPTIMISTIC", "1") != "0"
+
+
+def _forward_stages(V, lib, prm, g, geom, radii, img, out, P, W, H, dev, what):
+    """-> (num_rendered, binning workspace).  Both stages of the forward."""
+    st = _stream(dev)
+    n = C.c_int64(0)
+    hist = _R_HISTORY.get((V, W, H)) if _OPTIMISTIC else None
+    if hist is not None and hist[0] > 0:
+        cap = int(hist[0] * (P / hist[1]) * 1.25) + 65536
+        binning = torch.empty(lib.pg_raster_binning_bytes(V, W, H, cap), dtype=torch.uint8, device=dev)
+        rc = lib.pg_raster_forward_optimistic(C.byref(prm), C.byref(g), geom.data_ptr(), geom.numel(), radii.data_ptr(),
+                                              binning.data_ptr(), binning.numel(), cap, img.data_ptr(), C.byref(out),
+                                              C.byref(n), st)
+        rendered = int(n.value)
+        if rc == L.PG_OK:
+            _R_HISTORY[(V, W, H)] = (rendered, P)
+            return rendered, binning
+        if rc != 4 and rc != 3:     # PG_ERR_WORKSPACE: guess too small (stage 2 again below); 3: not on the band path
+            L.check(rc, what + " (optimistic)")
+        if rc == 3:
+            _R_HISTORY[(V, W, H)] = (0, P)
+            L.check(lib.pg_raster_forward_stage1(C.byref(prm), C.byref(g), geom.data_ptr(), geom.numel(),
+                                                 radii.data_ptr(), C.byref(n), st), what + " (stage 1)")
+            rendered = int(n.value)
+    else:
+        L.check(lib.pg_raster_forward_stage1(C.byref(prm), C.byref(g), geom.data_ptr(), geom.numel(),
+                                             radii.data_ptr(), C.byref(n), st), what + " (stage 1)")
+        rendered = int(n.value)
+        if hist is None:
+            _R_HISTORY[(V, W, H)] = (rendered, P)
+    binning = torch.empty(lib.pg_raster_binning_bytes(V, W, H, rendered), dtype=torch.uint8, device=dev)
+    L.check(lib.pg_raster_forward_stage2(C.byref(prm), C.byref(g), geom.data_ptr(), binning.data_ptr(),
+                                         binning.numel(), img.data_ptr(), rendered, C.byref(out), st), what + " (stage 2)")
+    if _R_HISTORY.get((V, W, H), (0, 0))[0] > 0:
+        _R_HISTORY[(V, W, H)] = (rendered, P)
+    return rendered, binning
 
 
 def _params(variant, P, W, H, tanx, tany, mod, prefiltered, debug, degree, M, bg, view, proj, proj_raw, campos,
@@ -70,7 +115,7 @@ def mark_visible(means3D, viewmatrix, projmatrix, variant=L.PG_VARIANT_3DGS):
     present = torch.zeros(P, dtype=torch.bool, device=means3D.device)
     if P:
         means3D, viewmatrix, projmatrix = _f32c(means3D), _f32c(viewmatrix), _f32c(projmatrix)
-        with torch.cuda.device(means3D.device):
+        with _guard(means3D.device):
             L.check(lib.pg_mark_visible(variant, P, L.ptr(means3D), L.ptr(viewmatrix), L.ptr(projmatrix),
                                         present.data_ptr(), _stream(means3D.device)), "mark_visible")
     return present
@@ -95,11 +140,10 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     radii = alloc(P, dtype=torch.int32, device=dev)
     n_touched = torch.zeros(P, dtype=torch.int32, device=dev)
     bopt = dict(dtype=torch.uint8, device=dev)
-    geom = torch.empty(0, **bopt)
-    binning = torch.empty(0, **bopt)
-    img = torch.empty(0, **bopt)
     rendered = 0
-    if P != 0:
+    if P == 0:
+        geom, binning, img = torch.empty(0, **bopt), torch.empty(0, **bopt), torch.empty(0, **bopt)
+    else:
         M = sh.size(1) if sh.numel() != 0 else 0
         background, means3D, colors, opacity = _f32c(background), _f32c(means3D), _f32c(colors), _f32c(opacity)
         scales, rotations, cov3D_precomp, sh = _f32c(scales), _f32c(rotations), _f32c(cov3D_precomp), _f32c(sh)
@@ -107,21 +151,14 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         prm = _params(L.PG_VARIANT_3DGS, P, W, H, tan_fovx, tan_fovy, scale_modifier, prefiltered, debug, degree, M,
                       background, viewmatrix, projmatrix, projmatrix_raw, campos)
         g = _gauss(means3D, sh, colors, opacity, scales, rotations, cov3D_precomp)
-        with torch.cuda.device(dev):
-            st = _stream(dev)
+        with _guard(dev):
             geom = torch.empty(lib.pg_raster_geom_bytes(L.PG_VARIANT_3DGS, P), **bopt)
             img = torch.empty(lib.pg_raster_image_bytes(L.PG_VARIANT_3DGS, W, H), **bopt)
-            n = C.c_int64(0)
-            L.check(lib.pg_raster_forward_stage1(C.byref(prm), C.byref(g), geom.data_ptr(), geom.numel(),
-                                                 radii.data_ptr(), C.byref(n), st), "raster forward (stage 1)")
-            rendered = int(n.value)
-            binning = torch.empty(lib.pg_raster_binning_bytes(L.PG_VARIANT_3DGS, W, H, rendered), **bopt)
             out = L.PgRasterFwdOut()
             out.out_color, out.out_depth, out.out_opacity = out_color.data_ptr(), out_depth.data_ptr(), out_opacity.data_ptr()
             out.radii, out.n_touched = radii.data_ptr(), n_touched.data_ptr()
-            L.check(lib.pg_raster_forward_stage2(C.byref(prm), C.byref(g), geom.data_ptr(), binning.data_ptr(),
-                                                 binning.numel(), img.data_ptr(), rendered, C.byref(out), st),
-                    "raster forward (stage 2)")
+            rendered, binning = _forward_stages(L.PG_VARIANT_3DGS, lib, prm, g, geom, radii, img, out, P, W, H, dev,
+                                                "raster forward")
     return rendered, out_color, radii, geom, binning, img, out_depth, out_opacity, n_touched
 
 
@@ -181,7 +218,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         bo.dL_dscales, bo.dL_drotations = dL_dscales.data_ptr(), dL_drotations.data_ptr()
         bo.dL_dtau = dL_dtau.data_ptr()
         bo.dL_dtau_full = L.ptr(tau_full)
-        with torch.cuda.device(dev):
+        with _guard(dev):
             L.check(lib.pg_raster_backward(C.byref(prm), C.byref(g), geomBuffer.data_ptr(), L.ptr(binningBuffer),
                                            imageBuffer.data_ptr(), int(R), C.byref(bi), C.byref(bo), _stream(dev)),
                     "raster backward")
@@ -210,11 +247,10 @@ def rasterize_gaussians_surfel(background, means3D, colors, opacity, scales, rot
     radii = alloc(P, dtype=torch.int32, device=dev)
     contributions = torch.zeros(P, **fopt)
     bopt = dict(dtype=torch.uint8, device=dev)
-    geom = torch.empty(0, **bopt)
-    binning = torch.empty(0, **bopt)
-    img = torch.empty(0, **bopt)
     rendered = 0
-    if P != 0:
+    if P == 0:
+        geom, binning, img = torch.empty(0, **bopt), torch.empty(0, **bopt), torch.empty(0, **bopt)
+    else:
         V = L.PG_VARIANT_SURFEL
         M = sh.size(1) if sh.numel() != 0 else 0
         background, means3D, colors, opacity = _f32c(background), _f32c(means3D), _f32c(colors), _f32c(opacity)
@@ -224,21 +260,13 @@ def rasterize_gaussians_surfel(background, means3D, colors, opacity, scales, rot
         prm = _params(V, P, W, H, tan_fovx, tan_fovy, scale_modifier, prefiltered, debug, degree, M, background,
                       viewmatrix, projmatrix, projmatrix_raw, campos, patchbbox, prcppoint, config)
         g = _gauss(means3D, sh, colors, opacity, scales, rotations, cov3D_precomp)
-        with torch.cuda.device(dev):
-            st = _stream(dev)
+        with _guard(dev):
             geom = torch.empty(lib.pg_raster_geom_bytes(V, P), **bopt)
             img = torch.empty(lib.pg_raster_image_bytes(V, W, H), **bopt)
-            n = C.c_int64(0)
-            L.check(lib.pg_raster_forward_stage1(C.byref(prm), C.byref(g), geom.data_ptr(), geom.numel(),
-                                                 radii.data_ptr(), C.byref(n), st), "surfel forward (stage 1)")
-            rendered = int(n.value)
-            binning = torch.empty(lib.pg_raster_binning_bytes(V, W, H, rendered), **bopt)
             out = L.PgRasterFwdOut()
             out.out_color, out.out_depth, out.out_opacity = out_color.data_ptr(), out_depth.data_ptr(), out_opac.data_ptr()
             out.radii, out.out_normal, out.contributions = radii.data_ptr(), out_normal.data_ptr(), contributions.data_ptr()
-            L.check(lib.pg_raster_forward_stage2(C.byref(prm), C.byref(g), geom.data_ptr(), binning.data_ptr(),
-                                                 binning.numel(), img.data_ptr(), rendered, C.byref(out), st),
-                    "surfel forward (stage 2)")
+            rendered, binning = _forward_stages(V, lib, prm, g, geom, radii, img, out, P, W, H, dev, "surfel forward")
     return rendered, out_color, out_normal, out_depth, out_opac, radii, contributions, geom, binning, img
 
 
@@ -296,7 +324,7 @@ def rasterize_gaussians_surfel_backward(background, means3D, radii, colors, scal
         bo.dL_dscales, bo.dL_drotations = dL_dscales.data_ptr(), dL_drotations.data_ptr()
         bo.dL_dtau = dL_dtau.data_ptr()
         bo.dL_dtau_full = L.ptr(tau_full)
-        with torch.cuda.device(dev):
+        with _guard(dev):
             L.check(lib.pg_raster_backward(C.byref(prm), C.byref(g), geomBuffer.data_ptr(), L.ptr(binningBuffer),
                                            imageBuffer.data_ptr(), int(R), C.byref(bi), C.byref(bo), _stream(dev)),
                     "surfel backward")

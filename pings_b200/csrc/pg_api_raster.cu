@@ -63,8 +63,9 @@ int pg_mark_visible(int variant, int P, const float* means3D, const float* viewm
   return PG_OK;
 }
 
-int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, size_t geom_bytes,
-                             int32_t* radii, int64_t* num_rendered, void* stream) {
+// wait = false: everything is queued (count copy + event included) but the host does not wait for the count.
+static int stage1_impl(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, size_t geom_bytes,
+                       int32_t* radii, int64_t* num_rendered, void* stream, bool wait) {
   if (!params_ok(prm) || !g || !num_rendered) return PG_ERR_ARG;
   *num_rendered = 0;
   const int P = prm->P;
@@ -120,6 +121,7 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
     PG_CUDA(depth_order_and_offsets(ws, P, bin_fast_path(gx * gy), st, /*need_offsets=*/!band_path(gx, gy)));
   }
   PG_LAUNCH_CHECK(prm->debug, st);
+  if (!wait) return PG_OK;
   PG_CUDA(cudaEventSynchronize(g_slot.ev));
   const unsigned long long R = *g_slot.pinned;
   if (R > 0xfffffff0ull) return PG_ERR_UNSUPPORTED;
@@ -127,9 +129,16 @@ int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, vo
   return PG_OK;
 }
 
-int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, void* binning_ws,
-                             size_t binning_bytes, void* image_ws, int64_t num_rendered,
-                             const PgRasterFwdOut* out, void* stream) {
+int pg_raster_forward_stage1(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, size_t geom_bytes,
+                             int32_t* radii, int64_t* num_rendered, void* stream) {
+  return stage1_impl(prm, g, geom_ws, geom_bytes, radii, num_rendered, stream, true);
+}
+
+// num_rendered: what the binning workspace was carved for; cap: ~0 when num_rendered is the true count, else the
+// capacity the device-side count is checked against (optimistic launch).
+static int stage2_impl(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, void* binning_ws,
+                       size_t binning_bytes, void* image_ws, int64_t num_rendered, unsigned long long cap,
+                       const PgRasterFwdOut* out, void* stream) {
   if (!params_ok(prm) || !g || !out || num_rendered < 0) return PG_ERR_ARG;
   const bool surfel = prm->variant == PG_VARIANT_SURFEL;
   if (!image_ws || !out->out_color || !out->out_depth || !out->out_opacity) return PG_ERR_ARG;
@@ -149,7 +158,7 @@ int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, vo
   carve_image(prm->variant, W, H, image_ws, &iw);
   const uint32_t* point_list = nullptr;
   if (band_path(gx, gy) && num_rendered > 0 && P > 0) {
-    PG_CUDA(bin_instances(gw, bw, iw, P, W, H, num_rendered, &point_list, st));   // times each kernel itself
+    PG_CUDA(bin_instances(gw, bw, iw, P, W, H, num_rendered, &point_list, st, cap));   // times each kernel itself
   } else {
     Phase ph("binning", st);
     PG_CUDA(bin_instances(gw, bw, iw, P, W, H, num_rendered, &point_list, st));
@@ -170,6 +179,30 @@ int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, vo
   }
   PG_LAUNCH_CHECK(prm->debug, st);
   return PG_OK;
+}
+
+int pg_raster_forward_stage2(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, void* binning_ws,
+                             size_t binning_bytes, void* image_ws, int64_t num_rendered,
+                             const PgRasterFwdOut* out, void* stream) {
+  return stage2_impl(prm, g, geom_ws, binning_ws, binning_bytes, image_ws, num_rendered, ~0ull, out, stream);
+}
+
+int pg_raster_forward_optimistic(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, size_t geom_bytes,
+                                 int32_t* radii, void* binning_ws, size_t binning_bytes, int64_t capacity,
+                                 void* image_ws, const PgRasterFwdOut* out, int64_t* num_rendered, void* stream) {
+  if (!params_ok(prm) || !num_rendered || capacity <= 0 || capacity > 0xfffffff0ll) return PG_ERR_ARG;
+  if (prm->P == 0) return PG_ERR_UNSUPPORTED;
+  if (!band_path(div_up(prm->image_width, kTile), div_up(prm->image_height, kTile))) return PG_ERR_UNSUPPORTED;
+  int rc = stage1_impl(prm, g, geom_ws, geom_bytes, radii, num_rendered, stream, false);
+  if (rc != PG_OK) return rc;
+  rc = stage2_impl(prm, g, geom_ws, binning_ws, binning_bytes, image_ws, capacity, (unsigned long long)capacity, out, stream);
+  if (rc != PG_OK) return rc;
+  // the ONE host wait of the forward, after everything is queued
+  PG_CUDA(cudaEventSynchronize(g_slot.ev));
+  const unsigned long long R = *g_slot.pinned;
+  if (R > 0xfffffff0ull) return PG_ERR_UNSUPPORTED;
+  *num_rendered = (int64_t)R;
+  return R > (unsigned long long)capacity ? PG_ERR_WORKSPACE : PG_OK;
 }
 
 int pg_raster_backward(const PgRasterParams* prm, const PgGaussians* g, void* geom_ws, void* binning_ws,

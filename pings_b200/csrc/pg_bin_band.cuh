@@ -64,9 +64,12 @@ template <bool WRITE>
 __global__ void __launch_bounds__(kBandWarps * 32) band_rows_kernel(
     int P, const uint32_t* __restrict__ nvalid, int NB, int GY, int nchunks, const uint32_t* __restrict__ sorted_idx,
     const uint2* __restrict__ srect, uint32_t* __restrict__ matA, const uint32_t* __restrict__ lstart,
-    uint32_t* __restrict__ recs, uint32_t* __restrict__ tickets) {
+    uint32_t* __restrict__ recs, uint32_t* __restrict__ tickets, const unsigned long long* __restrict__ total, unsigned long long cap) {
   pdl_trigger();
   pdl_wait();
+  // optimistic launch (pg_raster_forward_optimistic): workspace too small, or nothing visible - the host re-runs /
+  // the tile scan leaves empty ranges
+  { const unsigned long long t = *total; if (t > cap || t == 0) return; }
   // the count pass is the head of the chain: it also clears the two last-block tickets of the scan kernels
   if (!WRITE && blockIdx.x == 0 && threadIdx.x < 2) tickets[threadIdx.x] = 0u;
   // the depth sort dropped the culled Gaussians: V = *nvalid items, cut into nchunks equal chunks of whole 32-groups
@@ -144,9 +147,11 @@ __device__ __forceinline__ bool band_last_block(uint32_t* ticket) {
 // CTA that finishes last turns the totals into list starts and the segment table.
 __global__ void __launch_bounds__(256) band_list_scan_kernel(int nL, int nchunks, uint32_t* __restrict__ matA,
                                                              uint32_t* __restrict__ lcount, uint32_t* __restrict__ lstart,
-                                                             uint32_t* __restrict__ segbase, uint32_t* __restrict__ ticket) {
+                                                             uint32_t* __restrict__ segbase, uint32_t* __restrict__ ticket,
+                                                             const unsigned long long* __restrict__ total, unsigned long long cap) {
   pdl_trigger();
   pdl_wait();
+  { const unsigned long long t = *total; if (t > cap || t == 0) return; }
   {
     // CTA = list blockIdx.x; thread t owns entries [16 t, 16 t + 16) of the row (nchunks <= 4096, multiple of 8)
     uint32_t* row = matA + (size_t)blockIdx.x * nchunks;
@@ -241,11 +246,13 @@ template <bool WRITE>
 __global__ void __launch_bounds__(kBandWarps * 32) band_expand_kernel(
     int nL, int NB, const uint32_t* __restrict__ lstart, const uint32_t* __restrict__ segbase,
     const uint32_t* __restrict__ recs, const uint2* __restrict__ rect, uint32_t* __restrict__ tilemat,
-    const uint32_t* __restrict__ tiletot, const uint32_t* __restrict__ tilestart, uint32_t* __restrict__ out) {
+    const uint32_t* __restrict__ tiletot, const uint32_t* __restrict__ tilestart, uint32_t* __restrict__ out,
+    const unsigned long long* __restrict__ total, unsigned long long cap) {
   extern __shared__ uint32_t band_sm[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   pdl_trigger();
   pdl_wait();
+  { const unsigned long long t = *total; if (t > cap || t == 0) return; }
   uint32_t* sb = band_sm;                                      // [nL + 1]
   const int sb_words = (nL + 1 + 31) & ~31;
   // WRITE only: per warp [cap] staged words, [32] run deltas
@@ -325,11 +332,15 @@ __global__ void __launch_bounds__(256) band_tile_scan_kernel(int nL, int NB, int
                                                              const uint32_t* __restrict__ segbase,
                                                              uint32_t* __restrict__ tilemat, uint32_t* __restrict__ tiletot,
                                                              uint32_t* __restrict__ tilestart, uint2* __restrict__ ranges,
-                                                             uint32_t* __restrict__ ticket) {
+                                                             uint32_t* __restrict__ ticket, const unsigned long long* __restrict__ total, unsigned long long cap) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int slots = nL * kBandTiles;
   pdl_trigger();
   pdl_wait();
+  if (*total > cap || *total == 0) {   // workspace too small (or nothing visible): leave empty ranges so that the blend kernel that follows touches nothing
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < T; t += gridDim.x * blockDim.x) ranges[t] = make_uint2(0u, 0u);
+    return;
+  }
   for (int slot = blockIdx.x * 8 + warp; slot < slots; slot += gridDim.x * 8) {
     const int l = slot / kBandTiles, x = slot % kBandTiles;
     const uint32_t sb = segbase[l], nseg = segbase[l + 1] - sb;
@@ -368,8 +379,11 @@ __global__ void __launch_bounds__(256) band_tile_scan_kernel(int nL, int NB, int
   }
 }
 
+// total / cap: device-side instance count and the instance capacity the workspace was carved for (cap = ~0 when the
+// host already knows the count): every kernel leaves without writing when *total > cap.
 inline cudaError_t band_bin(const BandWs& w, int P, const uint32_t* nvalid, int gx, int gy, int64_t R, const uint32_t* sorted_idx,
-                            const uint2* srect, const uint2* rect, uint32_t* out, uint2* ranges, cudaStream_t st) {
+                            const uint2* srect, const uint2* rect, uint32_t* out, uint2* ranges, cudaStream_t st,
+                            const unsigned long long* total, unsigned long long cap) {
   const int NB = band_count(gx), nL = NB * gy, nchunks = band_row_chunks(nL), T = gx * gy;
   const size_t smA = (size_t)kBandWarps * (nL + gy + NB) * sizeof(uint32_t);
   const int sb_words = (nL + 1 + 31) & ~31;
@@ -401,23 +415,23 @@ inline cudaError_t band_bin(const BandWs& w, int P, const uint32_t* nvalid, int 
   // kernels are a programmatic-dependent-launch chain (pg_common.cuh); the head is a plain launch.
   {
     Phase ph("band_rows_kernel<count>", st);
-    band_rows_kernel<false><<<ctasA, thr, smA, st>>>(P, nvalid, NB, gy, nchunks, sorted_idx, srect, w.matA, cnull, null, w.ticket);
+    band_rows_kernel<false><<<ctasA, thr, smA, st>>>(P, nvalid, NB, gy, nchunks, sorted_idx, srect, w.matA, cnull, null, w.ticket, total, cap);
   }
   {
     Phase ph("band_list_scan_kernel", st);
-    e = launch_pdl(band_list_scan_kernel, (unsigned)nL, 256u, 0, st, nL, nchunks, w.matA, w.lcount, w.lstart, w.segbase, w.ticket);
+    e = launch_pdl(band_list_scan_kernel, (unsigned)nL, 256u, 0, st, nL, nchunks, w.matA, w.lcount, w.lstart, w.segbase, w.ticket, total, cap);
     if (e != cudaSuccess) return e;
   }
   {
     Phase ph("band_rows_kernel<write>", st);
     e = launch_pdl(band_rows_kernel<true>, (unsigned)ctasA, thr, smA, st, P, nvalid, NB, gy, nchunks, sorted_idx, srect,
-                   w.matA, (const uint32_t*)w.lstart, w.recs, w.ticket);
+                   w.matA, (const uint32_t*)w.lstart, w.recs, w.ticket, total, cap);
     if (e != cudaSuccess) return e;
   }
   {
     Phase ph("band_expand_kernel<count>", st);
     e = launch_pdl(band_expand_kernel<false>, (unsigned)(sms * 8), thr, smC, st, nL, NB, (const uint32_t*)w.lstart,
-                   (const uint32_t*)w.segbase, (const uint32_t*)w.recs, rect, w.tilemat, cnull, cnull, null);
+                   (const uint32_t*)w.segbase, (const uint32_t*)w.recs, rect, w.tilemat, cnull, cnull, null, total, cap);
     if (e != cudaSuccess) return e;
   }
   const int slots = nL * kBandTiles;
@@ -425,14 +439,14 @@ inline cudaError_t band_bin(const BandWs& w, int P, const uint32_t* nvalid, int 
   {
     Phase ph("band_tile_scan_kernel", st);
     e = launch_pdl(band_tile_scan_kernel, (unsigned)ctasT, 256u, 0, st, nL, NB, gx, T, (const uint32_t*)w.segbase, w.tilemat,
-                   w.tiletot, w.tilestart, ranges, w.ticket + 1);
+                   w.tiletot, w.tilestart, ranges, w.ticket + 1, total, cap);
     if (e != cudaSuccess) return e;
   }
   {
     Phase ph("band_expand_kernel<write>", st);
     e = launch_pdl(band_expand_kernel<true>, (unsigned)(sms * 3), thr, smW, st, nL, NB, (const uint32_t*)w.lstart,
                    (const uint32_t*)w.segbase, (const uint32_t*)w.recs, rect, w.tilemat, (const uint32_t*)w.tiletot,
-                   (const uint32_t*)w.tilestart, out);
+                   (const uint32_t*)w.tilestart, out, total, cap);
     if (e != cudaSuccess) return e;
   }
   (void)R;

@@ -486,13 +486,14 @@ inline cudaError_t depth_order_and_offsets(const GeomWs& ws, int P, bool fast, c
 
 // Emit + tile sort + ranges (stage 2 head). On return *point_list points at the sorted ids.
 inline cudaError_t bin_instances(const GeomWs& g, const BinWs& b, const ImageWs& im, int P, int W, int H,
-                                 int64_t R, const uint32_t** point_list, cudaStream_t st) {
+                                 int64_t R, const uint32_t** point_list, cudaStream_t st,
+                                 unsigned long long cap = ~0ull) {
   const int gx = div_up(W, kTile), gy = div_up(H, kTile);
   const int T = gx * gy;
   cudaError_t e = cudaSuccess;
   *point_list = b.valA;
   // the band binning writes the range of every tile itself
-  if (R > 0 && P > 0 && band_path(gx, gy)) return band_bin(b.band, P, g.nvalid, gx, gy, R, g.sorted_idx, g.srect, g.rect, b.valA, im.ranges, st);
+  if (R > 0 && P > 0 && band_path(gx, gy)) return band_bin(b.band, P, g.nvalid, gx, gy, R, g.sorted_idx, g.srect, g.rect, b.valA, im.ranges, st, g.total, cap);
   e = cudaMemsetAsync(im.ranges, 0, sizeof(uint2) * (size_t)T, st);
   if (e != cudaSuccess) return e;
   if (R <= 0 || P <= 0) return cudaSuccess;

@@ -16,7 +16,7 @@ class _PhotoDepthLoss(torch.autograd.Function):
         lib = L.lib()
         dev = rgb.device
         H, W = rgb.shape[-2], rgb.shape[-1]
-        f = lambda t: None if t is None else t.detach().to(torch.float32).contiguous()
+        f = lambda t: None if t is None else (t if (t.dtype is torch.float32 and t.is_contiguous()) else t.detach().to(torch.float32).contiguous())
         rgb_c, gt_c, d_c, gd_c, a_c = f(rgb), f(gt_rgb), f(depth), f(gt_depth), f(alpha)
         if d_c is None or gd_c is None:
             d_c = gd_c = a_c = None
@@ -24,12 +24,12 @@ class _PhotoDepthLoss(torch.autograd.Function):
         seed_d = torch.empty(H, W, dtype=torch.float32, device=dev) if d_c is not None else None
         sums = torch.empty(3, dtype=torch.float64, device=dev)
         loss = torch.empty(3, dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             L.check(lib.pg_photo_depth_loss_forward(H, W, rgb_c.data_ptr(), gt_c.data_ptr(), L.ptr(d_c), L.ptr(gd_c),
                                                     L.ptr(a_c), float(lambda_depth), float(depth_min), float(depth_max),
                                                     float(min_alpha), int(bool(inverse_depth)), seed_rgb.data_ptr(),
                                                     L.ptr(seed_d), sums.data_ptr(), loss.data_ptr(),
-                                                    torch.cuda.current_stream(dev).cuda_stream), "photo/depth loss")
+                                                    L.raw_stream(dev)), "photo/depth loss")
         ctx.save_for_backward(seed_rgb, seed_d, sums)
         ctx.meta = (H, W, float(lambda_depth), rgb.shape, None if depth is None else depth.shape)
         l_total, l_rgb, l_depth = loss.unbind(0)
@@ -46,10 +46,10 @@ class _PhotoDepthLoss(torch.autograd.Function):
         d_rgb = torch.empty(3, H, W, dtype=torch.float32, device=dev)
         want_d = seed_d is not None and ctx.needs_input_grad[2]
         d_depth = torch.empty(H, W, dtype=torch.float32, device=dev) if want_d else None
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             L.check(lib.pg_photo_depth_loss_backward(H, W, lam, up.data_ptr(), sums.data_ptr(), seed_rgb.data_ptr(),
                                                      L.ptr(seed_d), d_rgb.data_ptr(), L.ptr(d_depth),
-                                                     torch.cuda.current_stream(dev).cuda_stream), "photo/depth loss bwd")
+                                                     L.raw_stream(dev)), "photo/depth loss bwd")
         return (d_rgb.reshape(rgb_shape), None, None if d_depth is None else d_depth.reshape(depth_shape), None, None,
                 None, None, None, None, None)
 

@@ -345,3 +345,42 @@ def test_depth_order_bitexact_degenerate_depths(P, clusters, impl, monkeypatch):
     assert torch.equal(dv["point_list"], r["point_list"])
     assert torch.equal(dv["ranges"], r["ranges"])
     assert torch.equal(dv["n_contrib"], r["n_contrib"])
+
+
+@pytest.mark.gpu
+def test_optimistic_forward_capacity_guess_too_small_and_exact():
+    """pg_raster_forward_optimistic: the binning workspace is carved from the previous call's instance count.  A scene
+    with 30x more instances at the same image size overflows the guess (kernels must leave without writing, stage 2 is
+    re-run), the call after it fits; both must match the reference bit for bit, and so must the two-stage path."""
+    from oracle.ref_api import RefRaster3, available
+    from pings_b200 import _raster_c as RC
+    if not available("ref_r3"):
+        pytest.fail("oracle/_ref/libref_r3.so missing: run __graft_entry__.build() where /root/reference exists")
+    W, H = 400, 240
+    bg = torch.zeros(3, device="cuda")
+    ref = RefRaster3()
+    RC._R_HISTORY.pop((0, W, H), None)
+    counts = []
+    for P, seed, mul in ((20000, 31, 0.2), (20000, 32, 6.0), (20000, 32, 6.0), (500, 33, 1.0)):
+        cam, sc, mats, ct = _scene(P, W, H, seed)
+        sc["scales"] = (sc["scales"] * mul).contiguous()
+        view, full, proj, center = mats
+        R, color, radii, geom, binning, img, depth, opac, n_touched = _mine_forward(cam, sc, mats, W, H, bg)
+        r = ref.forward(sc, (view, full, proj), W, H, cam.tanfovx, cam.tanfovy, bg, campos=center)
+        assert R == r["num_rendered"] and R > 0
+        counts.append(R)
+        dv = RC.debug_views(0, P, W, H, R, geom, binning, img)
+        assert torch.equal(dv["point_list"], r["point_list"])
+        assert torch.equal(dv["ranges"], r["ranges"])
+        assert torch.equal(dv["n_contrib"], r["n_contrib"])
+        assert torch.equal(n_touched, r["n_touched"])
+        torch.testing.assert_close(color, r["color"], rtol=IMG_RTOL, atol=IMG_ATOL)
+        # and the backward reads the same workspace
+        e = torch.empty(0)
+        out = RC.rasterize_gaussians_backward(bg, sc["means3D"], radii, sc["colors_precomp"], sc["scales"], sc["rotations"],
+                                              1.0, e, view, full, proj, cam.tanfovx, cam.tanfovy, ct["color"], ct["depth"],
+                                              e, 0, center, geom, R, binning, img, False)
+        g = ref.backward(sc, (view, full, proj), cam.tanfovx, cam.tanfovy, bg, r["radii"], ct["color"], ct["depth"],
+                         campos=center)
+        assert _relmax(out[1], g["colors"]) < 1e-3
+    assert counts[1] > 10 * counts[0]          # the second call really overflowed the first call's guess
