@@ -268,9 +268,30 @@ def run_ours(args, rank, world, local):
     e = torch.empty(0)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     # two flat gradient buffers: the exchange of step k (side stream) overlaps the compute of step k+1
-    grads = [torch.zeros(P * 14, device=dev) for _ in range(2)]
+    # exchange buffers (double-buffered: the all-reduce of step k overlaps step k+1).  Default at N > 1: symmetric
+    # memory + our multimem kernel (in-switch reduction); PG_EXCHANGE=nccl keeps ncclAllReduce (also the fallback when
+    # the GPUs have no multicast support).
+    mm = None
+    if world > 1 and os.environ.get("PG_EXCHANGE", "multimem") != "nccl":
+        try:
+            from pings_b200.parallel import MultimemGradAllReduce
+            mm = [MultimemGradAllReduce(P * 14, dev, max_ctas=int(os.environ.get("PG_EXCHANGE_CTAS", "0"))) for _ in range(2)]
+        except Exception as ex_:   # noqa: BLE001  (no NVSwitch multicast: say so and use NCCL)
+            print(f"[bench] multimem exchange unavailable ({type(ex_).__name__}: {ex_}); using NCCL", file=sys.stderr)
+            mm = None
+        ok_ = torch.tensor([1 if mm is not None else 0], device=dev)
+        dist.all_reduce(ok_, op=dist.ReduceOp.MIN)
+        if int(ok_) == 0:
+            mm = None
+    grads = [m.flat for m in mm] if mm is not None else [torch.zeros(P * 14, device=dev) for _ in range(2)]
     grads_flat = grads[0]
-    side = torch.cuda.Stream(device=dev) if world > 1 else None
+
+    def exchange_grads(k: int):
+        if mm is not None:
+            mm[k].all_reduce()
+        else:
+            dist.all_reduce(grads[k])
+    side = torch.cuda.Stream(device=dev, priority=int(os.environ.get("PG_EXCHANGE_PRIO", "-1"))) if world > 1 else None
     step_no = [0]
     exch_ev: list = []
 
@@ -298,7 +319,7 @@ def run_ours(args, rank, world, local):
             with torch.cuda.stream(side):
                 ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 ea.record(side)
-                dist.all_reduce(flat)
+                exchange_grads((step_no[0] - 1) & 1)
                 eb.record(side)
                 exch_ev.append((ea, eb))
         return R
@@ -408,7 +429,7 @@ def run_ours(args, rank, world, local):
             cur.wait_stream(side)
             side.wait_stream(cur)
             with torch.cuda.stream(side):
-                dist.all_reduce(grads[i & 1])
+                exchange_grads(i & 1)
         res = torch.cat([loss.detach().view(1), rho.grad.flatten(), theta.grad.flatten()])
         host_out[slot].copy_(res, non_blocking=True)
         out_done[slot].record(cur)
@@ -502,7 +523,9 @@ def run_ours(args, rank, world, local):
                                "per GPU per step (BASELINE.json configs[1])",
                    "P": P, "W": W, "H": H, "num_rendered": int(R), "band_records": Q, "views_per_step": world,
                    "l2": "flushed between steps (256 MiB write)",
-                   "exchange": ("NCCL all-reduce of Gaussian-parameter grads (28 MB) on a side stream, overlapping the next "
+                   "exchange": ((("multimem all-reduce (our kernel: in-switch ld_reduce + multicast store over NVSwitch, "
+                                  "symmetric memory)") if mm is not None else "NCCL all-reduce")
+                                + " of Gaussian-parameter grads (28 MB) on a side stream, overlapping the next "
                                 "view's compute; the last one is timed as an exposed tail") if world > 1 else "none (N=1)",
                    "exchange_ms": round(exchange_ms, 4)},
         "clocks": clocks,
@@ -910,7 +933,7 @@ def mapping_leg(args, local, world, rank) -> dict:
     params = [npm.local_geo_features, npm.local_color_features]
     for d in list(decs.values()) + [sdf_dec]:
         params += [p for p in d.parameters()]
-    exchange = FlatGradAllReduce(params, average=False)
+    exchange = FlatGradAllReduce(params, average=False, multimem=os.environ.get("PG_EXCHANGE", "multimem") != "nccl")
     opt = FlatAdamW(exchange, lr=C4["lr"])
     info = {}
     nv = float(C4["views"])
@@ -973,7 +996,7 @@ def mapping_leg(args, local, world, rank) -> dict:
                              "neural_points": int(n), "local_points": int(npm.local_count()), "gaussians_per_point": K,
                              "gaussians_rendered_last_view": info.get("gaussians"),
                              "decoder": f"{Fg}+0/{Fc}+3 -> {Hd} x{Lv} -> K*out (5 heads); SDF [N,6,{Fg + 3}] -> 64 -> 1",
-                             "sdf_rows_per_rank": hi - lo, "exchange_bytes": exchange.nbytes if world > 1 else 0,
+                             "sdf_rows_per_rank": hi - lo, "exchange_bytes": exchange.nbytes if world > 1 else 0, "exchange_backend": exchange.backend if world > 1 else "none",
                              "loss_after_steps": round(float(lt), 6), "steps_run": steps + warm,
                              "replicas_in_sync": bool(in_sync),
                              "note": "map built by update() from one coloured C1-style scan at voxel 0.25 m; host-driven "

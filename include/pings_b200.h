@@ -348,6 +348,19 @@ size_t pg_spawn_count_index(int64_t NK);
 int pg_spawn_epilogue_forward(const PgSpawnArgs* args, const PgSpawnOut* out, void* stream);
 int pg_spawn_epilogue_backward(const PgSpawnArgs* args, const PgSpawnGrads* grads, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Gradient exchange of the data-parallel step (the reference is single-GPU, SURVEY.md 0.3, so
+ * there is no reference symbol): in-place all-reduce (sum, then * scale) of a flat fp32 buffer that lives in
+ * SYMMETRIC memory mapped for NVSwitch multicast on every rank, as ONE kernel: cross-GPU start barrier over the
+ * signal pads, multimem.ld_reduce of this rank's 1/world slice (the switch adds the replicas), multimem.st of the
+ * sum to all replicas, end barrier.  multicast_ptr: this rank's multicast address of element 0 (16-byte aligned);
+ * signal_pad_ptrs_dev: device array [world] of pointers to the ranks' zero-initialised signal pads of
+ * signal_pad_bytes each (torch.distributed._symmetric_memory provides all three); numel % 4 == 0.  Every rank must
+ * call with the same numel / world / max_ctas (0 = 8), each on its own stream; calls on one buffer must not overlap.
+ * ---------------------------------------------------------------------------------------- */
+int pg_multimem_allreduce_f32(void* multicast_ptr, const void* signal_pad_ptrs_dev, size_t signal_pad_bytes, int64_t numel,
+                              int rank, int world, float scale, int max_ctas, void* stream);
+
 /* Allocation-free variant of pg_spawn_epilogue_forward.  It has NO counterpart in the reference: it was added
  * for callers that cannot allocate device memory (CUDA graph capture, tight serving
  * loops, harnesses that forbid cudaMalloc).  The look-back scratch (`out->state`, ignored here and may be NULL) lives

@@ -45,7 +45,12 @@ class FlatGradAllReduce:
     stream and `wait()` joins it, so that it overlaps independent backward work (the SDF branch).
     """
 
-    def __init__(self, params: Iterable[torch.Tensor], average: bool = True, group=None, side_stream: bool = False):
+    def __init__(self, params: Iterable[torch.Tensor], average: bool = True, group=None, side_stream: bool = False,
+                 multimem: bool = False):
+        """multimem=True (CUDA, world > 1; a collective call): the flat buffer is allocated in symmetric memory and the
+        exchange is `MultimemGradAllReduce`'s kernel (in-switch reduction over NVSwitch) instead of ncclAllReduce; when
+        the system has no multicast support on any rank the buffer silently stays a plain tensor reduced by NCCL
+        (`self.backend` says which)."""
         self.params = [p for p in params]
         if not self.params:
             raise ValueError("FlatGradAllReduce: no parameters")
@@ -55,11 +60,23 @@ class FlatGradAllReduce:
                 raise ValueError("FlatGradAllReduce: all parameters must share one device and dtype "
                                  f"(got {p.device}/{p.dtype} next to {dev}/{dt})")
         self.sizes = [p.numel() for p in self.params]
-        self.flat = torch.zeros(sum(self.sizes), dtype=dt, device=dev)
+        self._mm = None
+        if multimem and dev.type == "cuda" and dt == torch.float32 and world()[1] > 1:
+            try:
+                self._mm = MultimemGradAllReduce(sum(self.sizes), dev, group)
+            except Exception:   # noqa: BLE001
+                self._mm = None
+            ok = torch.tensor([1 if self._mm is not None else 0], device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+            if int(ok) == 0:
+                self._mm = None
+        self.backend = "multimem" if self._mm is not None else "collective"
+        self.flat = self._mm.flat if self._mm is not None else torch.zeros(sum(self.sizes), dtype=dt, device=dev)
         self.views = list(self.flat.split(self.sizes))
         self.average = average
         self.group = group
-        self.stream = torch.cuda.Stream(device=dev) if (side_stream and dev.type == "cuda") else None
+        # high priority: the exchange's few CTAs get SM slots ahead of the compute kernels they overlap
+        self.stream = torch.cuda.Stream(device=dev, priority=-1) if (side_stream and dev.type == "cuda") else None
         self._work = None
 
     def attach(self) -> None:
@@ -103,13 +120,17 @@ class FlatGradAllReduce:
         if self.stream is not None:
             self.stream.wait_stream(torch.cuda.current_stream(self.flat.device))
             with torch.cuda.stream(self.stream):
-                dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
-                if self.average:
-                    self.flat.div_(ws)
+                self._reduce(ws)
         else:
-            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
-            if self.average:
-                self.flat.div_(ws)
+            self._reduce(ws)
+
+    def _reduce(self, ws: int) -> None:
+        if self._mm is not None:
+            self._mm.all_reduce(scale=(1.0 / ws) if self.average else 1.0)   # the average is folded into the kernel
+            return
+        dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+        if self.average:
+            self.flat.div_(ws)
 
     def wait(self) -> None:
         """Join the collective and scatter the reduced gradients back into p.grad."""
@@ -126,6 +147,61 @@ class FlatGradAllReduce:
     def __call__(self) -> None:
         self.launch()
         self.wait()
+
+
+class MultimemGradAllReduce:
+    """The gradient exchange as ONE kernel over NVSwitch multicast instead of ncclAllReduce.
+
+    `flat` is a flat fp32 buffer in symmetric memory (torch.distributed._symmetric_memory does the plumbing: the
+    allocation, the handle exchange, the multicast mapping and the signal pads); producers write their gradients
+    straight into it (`param_grads_out=` of the rasterizer backward, FlatGradAllReduce.attach-style views) and
+    `all_reduce()` launches `pg_multimem_allreduce_f32` on the current stream: barrier, in-switch reduction of this
+    rank's slice (multimem.ld_reduce), broadcast (multimem.st), barrier.  Replicas receive identical bits.
+
+    Raises when the GPUs have no multicast support (no NVSwitch): the caller then uses FlatGradAllReduce (NCCL).
+    The constructor is a collective (rendezvous + a self-check against a known sum)."""
+
+    def __init__(self, numel: int, device, group=None, max_ctas: int = 0):
+        import torch.distributed._symmetric_memory as symm
+        from . import _lib as L
+        self._L = L
+        group = group if group is not None else dist.group.WORLD
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.numel = int(numel)
+        padded = (self.numel + 3) // 4 * 4
+        self.device = torch.device(device)
+        self._store = symm.empty(padded, dtype=torch.float32, device=self.device)
+        self._hdl = symm.rendezvous(self._store, group)
+        mc = int(self._hdl.multicast_ptr)
+        if mc == 0:
+            raise RuntimeError("MultimemGradAllReduce: no multicast support on this system (NVSwitch required)")
+        # the handle describes the allocation block: this tensor may sit at an offset inside it
+        self._mc = mc + (self._store.data_ptr() - int(self._hdl.buffer_ptrs[self.rank]))
+        self._pads = int(self._hdl.signal_pad_ptrs_dev)
+        self._pad_bytes = int(type(self._hdl).signal_pad_size)
+        self.max_ctas = int(max_ctas)
+        self.flat = self._store[:self.numel]
+        self._self_check()
+
+    def all_reduce(self, scale: float = 1.0) -> None:
+        """In place on `flat`, on torch's current stream of the buffer's device."""
+        L = self._L
+        with L.device_guard(self.device):
+            L.check(L.lib().pg_multimem_allreduce_f32(self._mc, self._pads, self._pad_bytes, self._store.numel(), self.rank,
+                                                      self.world, float(scale), self.max_ctas, L.raw_stream(self.device)),
+                    "multimem all-reduce")
+
+    def _self_check(self) -> None:
+        n = self._store.numel()
+        idx = torch.arange(n, device=self.device, dtype=torch.float32)
+        self._store.copy_((idx % 251.0) * float(self.rank + 1))
+        self.all_reduce()
+        want = (idx % 251.0) * float(self.world * (self.world + 1) // 2)
+        ok = bool(torch.equal(self._store, want))
+        self._store.zero_()
+        torch.cuda.synchronize(self.device)
+        if not ok:
+            raise RuntimeError("MultimemGradAllReduce: self-check failed (multicast mapping does not address this buffer)")
 
 
 class FlatAdamW:
