@@ -268,8 +268,26 @@ int pg_sdf_query(const PgNeuralMap* map, const PgQueryArgs* args, const PgMlp* m
       return launch(sdf_query_batch_kernel<decltype(cpl)::value, 32>);
     });
   }
+  // PG_SDF_IMPL=warp keeps the warp-per-query kernel for shapes the half-warp kernel also covers (A/B, parity tests)
+  static const int force_warp = [] { const char* e = getenv("PG_SDF_IMPL"); return (e && e[0] == 'w') ? 1 : 0; }();
+  if (!force_warp && sdf_half_supported(md, a, map->K)) {
+    // persistent grid = what is resident (a partial second wave of persistent CTAs would double the time)
+    static int per_sm = 0;
+    if (!per_sm) {
+      PG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sdf_query_half_kernel, kSdfWarps * 32, 0));
+      if (per_sm < 1) per_sm = 1;
+    }
+    long long blocks = ((N + 1) / 2 + kSdfWarps - 1) / kSdfWarps;
+    const long long cap = (long long)kSmCount * per_sm;
+    if (blocks > cap) blocks = cap;
+    Phase ph("sdf_query", st);
+    sdf_query_half_kernel<<<(unsigned)blocks, kSdfWarps * 32, 0, st>>>(m, a, md, sdf_scale, N, q, sdf,
+                                                                       reinterpret_cast<long long*>(nn_counts));
+    PG_LAUNCH_CHECK(0, st);
+    return PG_OK;
+  }
   long long blocks = (N + kSdfWarps - 1) / kSdfWarps;
-  const long long cap = (long long)kSmCount * 8;  // persistent CTAs: weights are staged once per CTA
+  const long long cap = (long long)kSmCount * 5;  // persistent CTAs (weights staged once per CTA): 5 resident per SM (48 registers)
   if (blocks > cap) blocks = cap;
   Phase ph("sdf_query", st);
   return with_cpl(map->K, [&](auto cpl) {

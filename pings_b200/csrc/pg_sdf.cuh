@@ -312,4 +312,176 @@ __global__ void __launch_bounds__(kSdfWarps * 32) sdf_query_batch_kernel(NpMapDe
   }
 }
 
+// ---- half-warp variant ---------------------------------------------------------------------------------------------
+// Two queries per warp (16 lanes each): the probe phase has the same work per query (K = 81 probes = 6 per lane), but
+// everything that is one instruction per WARP in the kernel above - the arg-min rounds (2 REDUX + bookkeeping per
+// round), the IDW normalisation, the gather loop, the decoder - now serves two queries.  The decoder is specialised
+// for the shape of Decoder.sdf with weighted_first (DEC:62-83: in = F + 3 <= 16, ONE hidden layer of 64, out = 1):
+// lane s of a half owns hidden units s, s+16, s+32, s+48 with their 4 x 16 first-layer weights in REGISTERS for the
+// life of the persistent warp, and the inputs arrive by shuffle (x_f lives in lane f), so a query's decoder is
+// 16 SHFL + 64 FMA + 4 SHFL, no shared memory.  Same arithmetic order as the kernel above for the hidden layer
+// (sequential over f, then the bias); the output sum is a 4-term partial per lane + 4 butterfly steps.
+constexpr int kSdfHalfCpl = 6;      // probes per lane: K <= 96
+constexpr int kSdfHalfIn = 16;      // in_dim = F_geo + 3 <= 16
+constexpr int kSdfHalfHid = 64;
+
+__host__ __device__ inline bool sdf_half_supported(const MlpDev& m, const NpQueryDev& a, int K) {
+  return a.weighted_first && m.levels == 1 && m.hidden == kSdfHalfHid && m.out_dim == 1 && m.in_dim <= kSdfHalfIn &&
+         m.in_dim == a.F_geo + 3 && K <= 16 * kSdfHalfCpl && a.nn_k <= 16;
+}
+
+__global__ void __launch_bounds__(kSdfWarps * 32) sdf_query_half_kernel(NpMapDev m, NpQueryDev a, MlpDev mlp, float sdf_scale,
+                                                                        long long N, const float* __restrict__ q,
+                                                                        float* __restrict__ sdf,
+                                                                        long long* __restrict__ nn_counts) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int s = lane & 15, hb = lane & 16;          // sub-lane, first lane of this half
+  const uint32_t hmask = 0xffffu << hb;
+  const int F = a.F_geo, Fo = F + 3, Din = mlp.in_dim;
+  // first-layer weights in shared memory as float4 over this lane's 4 hidden units: w1s[f][s] = W1[s + 16 t][f],
+  // t = 0..3 (zeros beyond Din: x_f is zero there too); consecutive lanes read consecutive 16-byte words.
+  // (In registers - 64 per thread - the kernel ran at 2 CTAs per SM and lost to the probe latency: 427 vs 570 M q/s.)
+  __shared__ float4 w1s[kSdfHalfIn * 16];
+  for (int i = threadIdx.x; i < kSdfHalfIn * 16; i += blockDim.x) {
+    const int f = i >> 4, ss = i & 15;
+    float v[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) v[t] = f < Din ? mlp.W[0][(size_t)(ss + 16 * t) * Din + f] : 0.f;
+    w1s[i] = make_float4(v[0], v[1], v[2], v[3]);
+  }
+  __syncthreads();
+  float b1[4], w2[4];
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const int u = s + 16 * t;
+    b1[t] = mlp.B[0] ? mlp.B[0][u] : 0.f;
+    w2[t] = mlp.W[1][u];
+  }
+  const float b2 = mlp.B[1] ? mlp.B[1][0] : 0.f;
+  // per-lane slot residues of the probes c*16 + s (the 64-bit deltas are recomputed on the rare slow path)
+  uint32_t dr[kSdfHalfCpl];
+#pragma unroll
+  for (int c = 0; c < kSdfHalfCpl; ++c) dr[c] = (c * 16 + s < m.K) ? (uint32_t)np_slot_of(m, np_hash_delta(m, c * 16 + s)) : 0u;
+  const uint32_t d32 = (uint32_t)m.buffer_size;
+  const long long pairs = (N + 1) / 2;
+  for (long long p = (long long)blockIdx.x * kSdfWarps + warp; p < pairs; p += (long long)gridDim.x * kSdfWarps) {
+    const long long n = 2 * p + (hb >> 4);
+    const bool live = n < N;
+    const long long nq = live ? n : N - 1;     // the idle half of an odd tail repeats the last query, stores nothing
+    const float qx = q[3 * nq], qy = q[3 * nq + 1], qz = q[3 * nq + 2];
+    // ---- probes (np_warp_knn, 16 lanes) ----
+    const long long h0 = np_hash_base(m, np_cell(qx, m.res), np_cell(qy, m.res), np_cell(qz, m.res));
+    const bool fast = m.buffer_size < (1ll << 31) && h0 > -(1ll << 62) && h0 < (1ll << 62);
+    const uint32_t b0 = fast ? (uint32_t)np_slot_of(m, h0) : 0u;
+    float cd[kSdfHalfCpl];
+    int ci[kSdfHalfCpl];
+    int cnt = 0;
+#pragma unroll
+    for (int c = 0; c < kSdfHalfCpl; ++c) {
+      cd[c] = kNpInvalidDist;
+      ci[c] = -1;
+      if (c * 16 + s < m.K) {
+        long long idx;
+        float d;
+        if (fast) {
+          uint32_t slot = b0 + dr[c];
+          if (slot >= d32) slot -= d32;
+          np_probe_slot(m, (long long)slot, qx, qy, qz, idx, d);
+        } else {
+          np_probe_h(m, (long long)((unsigned long long)h0 + (unsigned long long)np_hash_delta(m, c * 16 + s)), qx, qy, qz, idx, d);
+        }
+        if (idx >= 0) {
+          if (a.use_only_measured && a.free_mask[idx]) idx = -1;
+          if (idx >= 0 && a.use_only_valid && !a.valid_mask[idx]) idx = -1;
+          if (idx >= 0 && a.query_locally) idx = a.g2l[idx];
+        }
+        if (idx >= 0) {
+          cd[c] = d;
+          ci[c] = (int)idx;
+          ++cnt;
+        }
+      }
+    }
+    cnt = __reduce_add_sync(hmask, cnt);
+    // ---- nn_k nearest: arg-min rounds, ties -> lowest probe position (a stable sort, NP:565) ----
+    float sel_d = kNpInvalidDist;
+    int sel_i = -1;
+    const int rounds = min(a.nn_k, cnt);
+    const int rounds_w = max(rounds, __shfl_xor_sync(0xffffffffu, rounds, 16));
+    for (int j = 0; j < rounds_w; ++j) {
+      float bd = kNpInvalidDist * 2.f;
+      int bk = 0x7fffffff;
+#pragma unroll
+      for (int c = 0; c < kSdfHalfCpl; ++c) {
+        if (ci[c] >= 0 && cd[c] < bd) {
+          bd = cd[c];
+          bk = c * 16 + s;
+        }
+      }
+      const uint32_t mn = __reduce_min_sync(hmask, __float_as_uint(bd));
+      bk = (int)__reduce_min_sync(hmask, __float_as_uint(bd) == mn ? (uint32_t)bk : 0xffffffffu);
+      const int owner = bk & 15, slot = bk >> 4;
+      int oi = -1;
+#pragma unroll
+      for (int c = 0; c < kSdfHalfCpl; ++c)
+        if (c == slot) oi = ci[c];
+      oi = __shfl_sync(0xffffffffu, oi, hb + owner);
+      if (j < rounds) {
+        if (s == owner) {
+#pragma unroll
+          for (int c = 0; c < kSdfHalfCpl; ++c)
+            if (c == slot) ci[c] = -1;
+        }
+        if (s == j) {
+          sel_d = __uint_as_float(mn);
+          sel_i = oi;
+        }
+      }
+    }
+    // ---- IDW weights (np_idw_weight on 16 lanes; xor offsets < 16 stay inside the half) ----
+    float u = 0.f;
+    if (s < a.nn_k) {
+      u = sel_i >= 0 ? __fdiv_rn(1.0f, sel_d + kNpEps) : 0.f;
+      if (cnt == 0) u = kNpEps;
+    }
+    float us = u;
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) us += __shfl_xor_sync(0xffffffffu, us, o);
+    float w = s < a.nn_k ? __fdiv_rn(u, us) : 0.f;
+    if (sel_i < 0) w = 0.f;
+    if (s == 0 && live && nn_counts) nn_counts[n] = cnt;
+    // ---- weighted feature vector: x_f in lane f (f < F: feature, then the neighbour vector) ----
+    float3 nv = make_float3(0.f, 0.f, 0.f);
+    if (sel_i >= 0) nv = np_neighbor_vec(a, sel_i, qx, qy, qz);   // lane j: its own neighbour, once
+    float x = 0.f;
+    for (int j = 0; j < a.nn_k; ++j) {
+      const int idx = __shfl_sync(0xffffffffu, sel_i, hb + j);
+      const float wj = __shfl_sync(0xffffffffu, w, hb + j);
+      const float vx = __shfl_sync(0xffffffffu, nv.x, hb + j);
+      const float vy = __shfl_sync(0xffffffffu, nv.y, hb + j);
+      const float vz = __shfl_sync(0xffffffffu, nv.z, hb + j);
+      if (idx < 0 || s >= Fo) continue;
+      const float v = s < F ? a.geo[(size_t)idx * F + s] : (s == F ? vx : (s == F + 1 ? vy : vz));
+      x += v * wj;
+    }
+    // ---- decoder: 16 -> 64 -> 1 ----
+    float h[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int f = 0; f < kSdfHalfIn; ++f) {
+      const float xf = __shfl_sync(0xffffffffu, x, hb + f);
+      const float4 wv = w1s[f * 16 + s];
+      h[0] += xf * wv.x;
+      h[1] += xf * wv.y;
+      h[2] += xf * wv.z;
+      h[3] += xf * wv.w;
+    }
+    float part = 0.f;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) part += mlp_act(h[t] + b1[t], mlp.leaky) * w2[t];
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+    if (s == 0 && live) sdf[n] = (part + b2) * sdf_scale;
+  }
+}
+
 }  // namespace pg
