@@ -270,7 +270,7 @@ int pg_sdf_query(const PgNeuralMap* map, const PgQueryArgs* args, const PgMlp* m
   }
   // PG_SDF_IMPL=warp keeps the warp-per-query kernel for shapes the half-warp kernel also covers (A/B, parity tests)
   static const int force_warp = [] { const char* e = getenv("PG_SDF_IMPL"); return (e && e[0] == 'w') ? 1 : 0; }();
-  if (!force_warp && sdf_half_supported(md, a, map->K)) {
+  if (!force_warp && sdf_half_supported(md, a, map->K) && map->n_points < (1ll << 31)) {
     // persistent grid = what is resident (a partial second wave of persistent CTAs would double the time)
     static int per_sm = 0;
     if (!per_sm) {

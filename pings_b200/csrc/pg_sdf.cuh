@@ -324,10 +324,11 @@ __global__ void __launch_bounds__(kSdfWarps * 32) sdf_query_batch_kernel(NpMapDe
 constexpr int kSdfHalfCpl = 6;      // probes per lane: K <= 96
 constexpr int kSdfHalfIn = 16;      // in_dim = F_geo + 3 <= 16
 constexpr int kSdfHalfHid = 64;
+constexpr int kSdfHalfSlots = 16 * kSdfHalfCpl;   // probe slots of a half-warp
 
 __host__ __device__ inline bool sdf_half_supported(const MlpDev& m, const NpQueryDev& a, int K) {
   return a.weighted_first && m.levels == 1 && m.hidden == kSdfHalfHid && m.out_dim == 1 && m.in_dim <= kSdfHalfIn &&
-         m.in_dim == a.F_geo + 3 && K <= 16 * kSdfHalfCpl && a.nn_k <= 16;
+         m.in_dim == a.F_geo + 3 && K <= 16 * kSdfHalfCpl && a.nn_k <= 16;   // (+ n_points < 2^31, checked by the caller)
 }
 
 __global__ void __launch_bounds__(kSdfWarps * 32) sdf_query_half_kernel(NpMapDev m, NpQueryDev a, MlpDev mlp, float sdf_scale,
@@ -342,6 +343,12 @@ __global__ void __launch_bounds__(kSdfWarps * 32) sdf_query_half_kernel(NpMapDev
   // t = 0..3 (zeros beyond Din: x_f is zero there too); consecutive lanes read consecutive 16-byte words.
   // (In registers - 64 per thread - the kernel ran at 2 CTAs per SM and lost to the probe latency: 427 vs 570 M q/s.)
   __shared__ float4 w1s[kSdfHalfIn * 16];
+  // per half-warp scratch: occupied slots (index, probe position), surviving candidates (key, index), the nn_k kept
+  __shared__ uint32_t sh_hit[2 * kSdfHalfSlots * kSdfWarps * 2];
+  __shared__ unsigned long long sh_key[kSdfHalfSlots * kSdfWarps * 2];
+  __shared__ uint32_t sh_val[kSdfHalfSlots * kSdfWarps * 2];
+  __shared__ float sh_outd[16 * kSdfWarps * 2];
+  __shared__ int sh_outi[16 * kSdfWarps * 2];
   for (int i = threadIdx.x; i < kSdfHalfIn * 16; i += blockDim.x) {
     const int f = i >> 4, ss = i & 15;
     float v[4];
@@ -369,75 +376,111 @@ __global__ void __launch_bounds__(kSdfWarps * 32) sdf_query_half_kernel(NpMapDev
     const bool live = n < N;
     const long long nq = live ? n : N - 1;     // the idle half of an odd tail repeats the last query, stores nothing
     const float qx = q[3 * nq], qy = q[3 * nq + 1], qz = q[3 * nq + 2];
-    // ---- probes (np_warp_knn, 16 lanes) ----
+    // ---- phase 1: the slot-table probes (6 independent loads per lane), optional time filter ----
     const long long h0 = np_hash_base(m, np_cell(qx, m.res), np_cell(qy, m.res), np_cell(qz, m.res));
     const bool fast = m.buffer_size < (1ll << 31) && h0 > -(1ll << 62) && h0 < (1ll << 62);
     const uint32_t b0 = fast ? (uint32_t)np_slot_of(m, h0) : 0u;
-    float cd[kSdfHalfCpl];
-    int ci[kSdfHalfCpl];
-    int cnt = 0;
+    int pidx[kSdfHalfCpl];
 #pragma unroll
     for (int c = 0; c < kSdfHalfCpl; ++c) {
-      cd[c] = kNpInvalidDist;
-      ci[c] = -1;
+      pidx[c] = -1;
       if (c * 16 + s < m.K) {
-        long long idx;
-        float d;
+        long long slot;
         if (fast) {
-          uint32_t slot = b0 + dr[c];
-          if (slot >= d32) slot -= d32;
-          np_probe_slot(m, (long long)slot, qx, qy, qz, idx, d);
+          uint32_t sl = b0 + dr[c];
+          if (sl >= d32) sl -= d32;
+          slot = (long long)sl;
         } else {
-          np_probe_h(m, (long long)((unsigned long long)h0 + (unsigned long long)np_hash_delta(m, c * 16 + s)), qx, qy, qz, idx, d);
+          slot = np_slot_of(m, (long long)((unsigned long long)h0 + (unsigned long long)np_hash_delta(m, c * 16 + s)));
         }
-        if (idx >= 0) {
-          if (a.use_only_measured && a.free_mask[idx]) idx = -1;
-          if (idx >= 0 && a.use_only_valid && !a.valid_mask[idx]) idx = -1;
-          if (idx >= 0 && a.query_locally) idx = a.g2l[idx];
-        }
-        if (idx >= 0) {
-          cd[c] = d;
-          ci[c] = (int)idx;
-          ++cnt;
-        }
+        pidx[c] = m.table32 ? m.table32[slot] : (int)m.table[slot];
       }
     }
-    cnt = __reduce_add_sync(hmask, cnt);
-    // ---- nn_k nearest: arg-min rounds, ties -> lowest probe position (a stable sort, NP:565) ----
-    float sel_d = kNpInvalidDist;
-    int sel_i = -1;
-    const int rounds = min(a.nn_k, cnt);
-    const int rounds_w = max(rounds, __shfl_xor_sync(0xffffffffu, rounds, 16));
-    for (int j = 0; j < rounds_w; ++j) {
-      float bd = kNpInvalidDist * 2.f;
-      int bk = 0x7fffffff;
+    if (m.time_filtering) {
 #pragma unroll
       for (int c = 0; c < kSdfHalfCpl; ++c) {
-        if (ci[c] >= 0 && cd[c] < bd) {
-          bd = cd[c];
-          bk = c * 16 + s;
-        }
-      }
-      const uint32_t mn = __reduce_min_sync(hmask, __float_as_uint(bd));
-      bk = (int)__reduce_min_sync(hmask, __float_as_uint(bd) == mn ? (uint32_t)bk : 0xffffffffu);
-      const int owner = bk & 15, slot = bk >> 4;
-      int oi = -1;
-#pragma unroll
-      for (int c = 0; c < kSdfHalfCpl; ++c)
-        if (c == slot) oi = ci[c];
-      oi = __shfl_sync(0xffffffffu, oi, hb + owner);
-      if (j < rounds) {
-        if (s == owner) {
-#pragma unroll
-          for (int c = 0; c < kSdfHalfCpl; ++c)
-            if (c == slot) ci[c] = -1;
-        }
-        if (s == j) {
-          sel_d = __uint_as_float(mn);
-          sel_i = oi;
+        if (pidx[c] >= 0) {
+          const float diff = fabsf(m.travel[m.cur_ts] - m.travel[m.ts_create[pidx[c]]]);
+          if (!(diff < m.diff_local)) pidx[c] = -1;
         }
       }
     }
+    // ---- phase 2: compact the occupied slots of each half (about 8 of 81) into shared memory, in probe order ----
+    uint32_t* hit_i = sh_hit + (size_t)(warp * 2 + (hb >> 4)) * kSdfHalfSlots;
+    uint32_t* hit_p = hit_i + kSdfHalfSlots * kSdfWarps * 2;
+    uint32_t nhit = 0;
+    const uint32_t below = (1u << s) - 1u;
+#pragma unroll
+    for (int c = 0; c < kSdfHalfCpl; ++c) {
+      const bool hit = pidx[c] >= 0;
+      const uint32_t bm = (__ballot_sync(0xffffffffu, hit) >> hb) & 0xffffu;
+      if (hit) {
+        const uint32_t r = nhit + __popc(bm & below);
+        hit_i[r] = (uint32_t)pidx[c];
+        hit_p[r] = (uint32_t)(c * 16 + s);
+      }
+      nhit += __popc(bm);
+    }
+    __syncwarp();
+    // ---- phase 3: distances only for the occupied slots (np_probe_slot's arithmetic), masks, local index; the
+    //      surviving candidates are compacted again as (dist bits << 32 | probe position, index) ----
+    unsigned long long* ck = sh_key + (size_t)(warp * 2 + (hb >> 4)) * kSdfHalfSlots;
+    uint32_t* cv = sh_val + (size_t)(warp * 2 + (hb >> 4)) * kSdfHalfSlots;
+    uint32_t ncand = 0;
+    const uint32_t nhit_w = max(nhit, __shfl_xor_sync(0xffffffffu, nhit, 16));
+    for (uint32_t t0 = 0; t0 < nhit_w; t0 += 16) {
+      const uint32_t t = t0 + s;
+      long long idx = -1;
+      float d = 0.f;
+      uint32_t pos = 0;
+      if (t < nhit) {
+        idx = (long long)hit_i[t];
+        pos = hit_p[t];
+        const float sx = __fsub_rn(m.pts[3 * idx + 0], qx);
+        const float sy = __fsub_rn(m.pts[3 * idx + 1], qy);
+        const float sz = __fsub_rn(m.pts[3 * idx + 2], qz);
+        d = __fadd_rn(__fadd_rn(__fmul_rn(sx, sx), __fmul_rn(sy, sy)), __fmul_rn(sz, sz));
+        if (d > m.max_valid) idx = -1;
+        if (idx >= 0 && a.use_only_measured && a.free_mask[idx]) idx = -1;
+        if (idx >= 0 && a.use_only_valid && !a.valid_mask[idx]) idx = -1;
+        if (idx >= 0 && a.query_locally) idx = a.g2l[idx];
+      }
+      const bool ok = idx >= 0;
+      const uint32_t bm = (__ballot_sync(0xffffffffu, ok) >> hb) & 0xffffu;
+      if (ok) {
+        const uint32_t r = ncand + __popc(bm & below);
+        ck[r] = ((unsigned long long)__float_as_uint(d) << 32) | (unsigned long long)pos;
+        cv[r] = (uint32_t)idx;
+      }
+      ncand += __popc(bm);
+    }
+    __syncwarp();
+    const int cnt = (int)ncand;
+    // ---- phase 4: the nn_k nearest by rank counting: rank = number of candidates with a smaller (distance, probe
+    //      position) key - the stable order of torch.sort over the probe axis (NP:565); keys are unique ----
+    float* od = sh_outd + (size_t)(warp * 2 + (hb >> 4)) * 16;
+    int* oi = sh_outi + (size_t)(warp * 2 + (hb >> 4)) * 16;
+    const uint32_t ncand_w = max(ncand, __shfl_xor_sync(0xffffffffu, ncand, 16));
+    for (uint32_t t0 = 0; t0 < ncand_w; t0 += 16) {
+      const uint32_t t = t0 + s;
+      if (t < ncand) {
+        const unsigned long long key = ck[t];
+        uint32_t rank = 0;
+        for (uint32_t k = 0; k < ncand; ++k) rank += ck[k] < key ? 1u : 0u;
+        if (rank < (uint32_t)a.nn_k) {
+          od[rank] = __uint_as_float((uint32_t)(key >> 32));
+          oi[rank] = (int)cv[t];
+        }
+      }
+    }
+    __syncwarp();
+    float sel_d = kNpInvalidDist;
+    int sel_i = -1;
+    if (s < min(a.nn_k, cnt)) {
+      sel_d = od[s];
+      sel_i = oi[s];
+    }
+    __syncwarp();   // the next query of this warp overwrites the shared arrays
     // ---- IDW weights (np_idw_weight on 16 lanes; xor offsets < 16 stay inside the half) ----
     float u = 0.f;
     if (s < a.nn_k) {

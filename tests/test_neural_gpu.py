@@ -179,3 +179,34 @@ def test_query_certainty_matches_reference_golden():
     assert np.array_equal(c1.cpu().numpy(), G["certainty.value"])
     assert np.array_equal(c2.cpu().numpy(), G["certainty.value_default_nbh"])
     assert float(c1[:20].abs().max()) == 0.0 and float(c1.max()) > 0.0
+
+
+def test_fused_sdf_dense_volume_many_candidates():
+    """A volume filled at the voxel size: nearly every one of the 81 probed cells holds a point, so a query has far
+    more than 16 occupied slots - the half-warp SDF kernel's multi-pass distance / rank-counting path.  nn_counts
+    bit-exact against the CPU oracle, SDF within the usual tolerance."""
+    from pings_b200.decoder import Decoder
+    from pings_b200.neural_points import NeuralPoints, default_config
+    from pings_b200 import synth_neural as SN
+    g = torch.Generator().manual_seed(5)
+    cfg = default_config(device="cuda", buffer_size=int(2e6), track_on=False, temporal_local_map_off=True)
+    res = cfg.voxel_size_m
+    n = 14
+    ii = torch.stack(torch.meshgrid(*[torch.arange(n, dtype=torch.float32)] * 3, indexing="ij"), -1).reshape(-1, 3)
+    pts = ((ii + 0.5 + 0.3 * (torch.rand(ii.shape, generator=g) - 0.5)) * res).contiguous()
+    npm = NeuralPoints(cfg)
+    npm.travel_dist = torch.zeros(1, device="cuda")
+    npm.update(pts.cuda(), None, None, torch.zeros(3, device="cuda"), None, 0)
+    npm.geo_features = (0.1 * torch.randn(npm.count() + 1, cfg.feature_dim, generator=g)).cuda()
+    npm.reset_local_map(torch.zeros(3, device="cuda"), None, 0)
+    torch.manual_seed(3)
+    dec = Decoder(cfg, cfg.feature_dim, 64, 1, 1).cuda()
+    q = (torch.rand(6001, 3, generator=g) * (n * res)).contiguous()      # odd count: the idle half of the last pair
+    S = SN.oracle_state(npm)
+    d2o, idxo = O.radius_search(S, q, False)
+    assert int((idxo >= 0).sum(1).max()) > 16                              # more candidates than a half-warp has lanes
+    sdf, _, cnt = npm.sdf_fused(q.cuda(), dec)
+    Ws, Bs = [l.weight.detach().cpu() for l in dec._linears()], [l.bias.detach().cpu() for l in dec._linears()]
+    so, _, co = O.sdf_query(S, q, cfg.query_nn_k, True, Ws, Bs, dec.sdf_scale, time_filtering=False)
+    assert torch.equal(cnt.cpu(), co)
+    np.testing.assert_allclose(sdf.cpu().numpy(), so.numpy(), rtol=RTOL, atol=ATOL)
