@@ -394,11 +394,17 @@ def run_ours(args, rank, world, local):
     ready = [torch.cuda.Event() for _ in range(2)]
     consumed = [torch.cuda.Event() for _ in range(2)]
 
+    h2d_ev: list = []
+
     def upload(i: int):
         slot = i & 1
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(consumed[slot])
+            ta, tb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ta.record(copy_stream)
             slots_flat[slot].copy_(pinned_flat, non_blocking=True)
+            tb.record(copy_stream)
+            h2d_ev.append((ta, tb))
             ready[slot].record(copy_stream)
 
     def step_e2e(i: int, prefetch: bool, more: bool = True):
@@ -479,7 +485,15 @@ def run_ours(args, rank, world, local):
         return float(t.item()) / args.steps
 
     e2e_serial_ms = run_e2e(False)
+    h2d_ev.clear()
     e2e_ms_per_step = run_e2e(True)
+    torch.cuda.synchronize()
+    h2d_ms = sorted(x.elapsed_time(y) for x, y in h2d_ev[-args.steps:])
+    h2d_ms = h2d_ms[len(h2d_ms) // 2] if h2d_ms else 0.0       # median device time of one step's upload
+    t_ = torch.tensor([h2d_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+    h2d_ms = float(t_.item())
     if os.environ.get("PG_E2E_PROFILE") and rank == 0:   # dev only: where the pipelined step's host and device time go
         from torch.profiler import ProfilerActivity, profile
         with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
@@ -531,6 +545,7 @@ def run_ours(args, rank, world, local):
         "clocks": clocks,
         "e2e": {"value": round(e2e_value, 2), "unit": "Mpix/s", "ms_per_step": round(e2e_ms_per_step, 4),
                 "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 28,
+                "h2d_ms": round(h2d_ms, 4), "h2d_gbs": round(h2d_bytes / (h2d_ms * 1e-3) / 1e9, 1) if h2d_ms > 0 else None,
                 "staging": "pipelined loop: H2D of step k+1 on a copy stream overlaps step k, the host reads step k's "
                            "result (loss + pose gradient, pinned D2H) while step k+1 runs; L2 flush between steps "
                            "inside the timed region; serial_value = copy, compute, read back to back",
