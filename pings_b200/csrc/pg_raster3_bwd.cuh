@@ -8,6 +8,9 @@
 #pragma once
 #include "pg_raster3_fwd.cuh"
 
+#ifndef PG_BWD_MIN_CTAS
+#define PG_BWD_MIN_CTAS 1   // 13 (72 registers, one wave at C2) measured slower: 0.157 vs 0.149 ms
+#endif
 namespace pg {
 
 // Sum 12 per-lane values over the 32 lanes of a warp with a halving butterfly:
@@ -66,7 +69,7 @@ struct RBwdSlab {
 //   gacc[3i+0] = (dL_dmean2D.x, dL_dmean2D.y, dL_dconic.x, dL_dconic.y)
 //   gacc[3i+1] = (dL_dconic.w, dL_dopacity, dL_ddepth, 0)
 //   gacc[3i+2] = (dL_dcolor.r, .g, .b, 0)
-__global__ void __launch_bounds__(kRThreads) r3_render_bwd_kernel(
+__global__ void __launch_bounds__(kRThreads, PG_BWD_MIN_CTAS) r3_render_bwd_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H, int gx,
     const float4* __restrict__ rec, const float* __restrict__ bg, const float* __restrict__ final_T,
     const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
