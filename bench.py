@@ -307,7 +307,7 @@ def run_ours(args, rank, world, local):
                                               sc["rotations"], 1.0, e, view, full, proj, cam.tanfovx, cam.tanfovy,
                                               ct["color"], ct["depth"], e, 0, center, geom, R, binning, img, False,
                                               param_grads_out=flat)
-        last_binning[:] = [binning, geom, img]
+        last_binning[:] = [binning, geom, img, RC.last_binning_capacity()]
         if world > 1 and exchange:
             # training exchange step: sum the Gaussian-parameter gradients over the view shards (the backward wrote
             # them straight into the flat buffer).  The all-reduce runs on a side stream and overlaps the next
@@ -517,7 +517,7 @@ def run_ours(args, rank, world, local):
     if rank != 0:
         return None
     phase_ms = {k: sum(v) / len(v) for k, v in phases.items()}
-    Q = int(L.lib().pg_raster_band_records(W, H, int(R), last_binning[0].data_ptr(), None)) if last_binning else -1
+    Q = int(L.lib().pg_raster_band_records(W, H, int(last_binning[3]), last_binning[0].data_ptr(), None)) if last_binning else -1
     BAND_LISTS["n"] = ((W + 15) // 16 + 31) // 32 * ((H + 15) // 16)
     ab = algorithmic_bytes(P, R, W, H, Q)
     pk = peaks()

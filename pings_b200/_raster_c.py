@@ -28,11 +28,19 @@ def _f32c(t: torch.Tensor) -> torch.Tensor:
 _stream = L.raw_stream
 _guard = L.device_guard
 
-# Instance-count history per (variant, W, H): (last count, Gaussians of that call).  The forward carves its binning
-# workspace for the predicted count (+ margin) and launches both stages before it waits for the true one
-# (pg_raster_forward_optimistic); a wrong guess costs one re-run of stage 2, never a wrong result.
+# Instance-count history per (variant, W, H): (instances per Gaussian - a slowly decaying maximum over the recent calls,
+# so that a batch of views that alternate does not overflow on every other view - and a validity flag).  The forward
+# carves its binning workspace for the predicted count (+ margin) and launches both stages before it waits for the
+# true one (pg_raster_forward_optimistic); a wrong guess costs one re-run of stage 2, never a wrong result.
 _R_HISTORY: dict = {}
 _OPTIMISTIC = os.environ.get("PG_RASTER_OPTIMISTIC", "1") != "0"
+_LAST_CAPACITY = [0]     # instance capacity the most recent forward's binning workspace was carved for (diagnostics)
+
+
+def last_binning_capacity() -> int:
+    """What `pg_raster_band_records` / any carve of the most recent forward's binning workspace must be given as
+    num_rendered (point_list itself sits at offset 0 whatever the capacity)."""
+    return _LAST_CAPACITY[0]
 
 
 def _forward_stages(V, lib, prm, g, geom, radii, img, out, P, W, H, dev, what):
@@ -41,19 +49,20 @@ def _forward_stages(V, lib, prm, g, geom, radii, img, out, P, W, H, dev, what):
     n = C.c_int64(0)
     hist = _R_HISTORY.get((V, W, H)) if _OPTIMISTIC else None
     if hist is not None and hist[0] > 0:
-        cap = int(hist[0] * (P / hist[1]) * 1.25) + 65536
+        cap = int(hist[0] * P * 1.25) + 65536
         binning = torch.empty(lib.pg_raster_binning_bytes(V, W, H, cap), dtype=torch.uint8, device=dev)
         rc = lib.pg_raster_forward_optimistic(C.byref(prm), C.byref(g), geom.data_ptr(), geom.numel(), radii.data_ptr(),
                                               binning.data_ptr(), binning.numel(), cap, img.data_ptr(), C.byref(out),
                                               C.byref(n), st)
         rendered = int(n.value)
         if rc == L.PG_OK:
-            _R_HISTORY[(V, W, H)] = (rendered, P)
+            _R_HISTORY[(V, W, H)] = (max(rendered / P, 0.97 * hist[0]), 1)
+            _LAST_CAPACITY[0] = cap
             return rendered, binning
         if rc != 4 and rc != 3:     # PG_ERR_WORKSPACE: guess too small (stage 2 again below); 3: not on the band path
             L.check(rc, what + " (optimistic)")
         if rc == 3:
-            _R_HISTORY[(V, W, H)] = (0, P)
+            _R_HISTORY[(V, W, H)] = (0, 0)
             L.check(lib.pg_raster_forward_stage1(C.byref(prm), C.byref(g), geom.data_ptr(), geom.numel(),
                                                  radii.data_ptr(), C.byref(n), st), what + " (stage 1)")
             rendered = int(n.value)
@@ -62,12 +71,14 @@ def _forward_stages(V, lib, prm, g, geom, radii, img, out, P, W, H, dev, what):
                                              radii.data_ptr(), C.byref(n), st), what + " (stage 1)")
         rendered = int(n.value)
         if hist is None:
-            _R_HISTORY[(V, W, H)] = (rendered, P)
+            _R_HISTORY[(V, W, H)] = (max(rendered / P, 1e-9), 1)
     binning = torch.empty(lib.pg_raster_binning_bytes(V, W, H, rendered), dtype=torch.uint8, device=dev)
     L.check(lib.pg_raster_forward_stage2(C.byref(prm), C.byref(g), geom.data_ptr(), binning.data_ptr(),
                                          binning.numel(), img.data_ptr(), rendered, C.byref(out), st), what + " (stage 2)")
-    if _R_HISTORY.get((V, W, H), (0, 0))[0] > 0:
-        _R_HISTORY[(V, W, H)] = (rendered, P)
+    _LAST_CAPACITY[0] = rendered
+    h_ = _R_HISTORY.get((V, W, H), (0, 0))
+    if h_[0] > 0:
+        _R_HISTORY[(V, W, H)] = (max(rendered / P, 0.97 * h_[0]), 1)
     return rendered, binning
 
 

@@ -187,11 +187,18 @@ __global__ void __launch_bounds__(256) depth2normal_bwd_kernel(D2NArgs a, const 
   // p_k = (P_k - P_c m_c) m_k
   const V3 du = v3mul(dPu, s.mu), dl = v3mul(dPl, s.ml), dr = v3mul(dPr, s.mr), db = v3mul(dPb, s.mb);
   const V3 dc = v3mul(v3add(v3add(du, dl), v3add(dr, db)), -s.mc);
-  atomicAdd(d_depth + i, v3dot(dc, s.ac));
-  atomicAdd(d_depth + s.iu, v3dot(du, s.au));
-  atomicAdd(d_depth + s.il, v3dot(dl, s.al));
-  atomicAdd(d_depth + s.ib, v3dot(db, s.ab));
-  atomicAdd(d_depth + s.ir, v3dot(dr, s.ar));
+  // At an image border the replicated neighbour IS the centre pixel, so its cotangent lands on this pixel too and
+  // cancels the same term inside dc.  The two are combined HERE, in registers, and reach memory as one atomic: when
+  // the normal degenerates (len = 0: border + a masked neighbour; G = dn / 1e-12 as F.normalize's eps gives) they
+  // are +-1e12, and scattered separately the order of the atomics decided how much of the neighbours' contributions
+  // survived (an intermittent 0.007 at one pixel of the parity test).  Inside dc the huge term still absorbs the
+  // small ones exactly as it does in the eager reference's fp32 sum (tests/golden/render_post.npz contains that).
+  float self = v3dot(dc, s.ac);
+  if (s.iu == i) self += v3dot(du, s.au); else atomicAdd(d_depth + s.iu, v3dot(du, s.au));
+  if (s.il == i) self += v3dot(dl, s.al); else atomicAdd(d_depth + s.il, v3dot(dl, s.al));
+  if (s.ib == i) self += v3dot(db, s.ab); else atomicAdd(d_depth + s.ib, v3dot(db, s.ab));
+  if (s.ir == i) self += v3dot(dr, s.ar); else atomicAdd(d_depth + s.ir, v3dot(dr, s.ar));
+  atomicAdd(d_depth + i, self);
 }
 
 // ---- affine exposure correction (GR:449-458): out = M rgb + offset per pixel ------------------------------------------

@@ -102,7 +102,18 @@ def test_depth2normal_and_exposure_kernels(H, W, scale):
     w = torch.randn(3, H, W, generator=g).cuda()
     (out * w).sum().backward()
     (ref * w).sum().backward()
-    torch.testing.assert_close(depth.grad, d2.grad, rtol=1e-3, atol=1e-4 * float(d2.grad.abs().max()))
+    # Pixels whose un-normalised normal is EXACTLY zero (a replicated border difference + a masked neighbour) are
+    # excluded: F.normalize's eps turns the cotangent into g / 1e-12 there, the eager graph then adds +X and -X
+    # (X ~ 1e12) into that pixel's depth gradient and whatever else was accumulated is absorbed - its value (0.0 on
+    # CPU) is an artefact.  Our kernel drops the analytically cancelling pair and keeps the neighbours' contributions.
+    with torch.no_grad():
+        r0 = _d2n_restatement(d2.detach(), mask, [0.48, 0.53], W * scale, H * scale, 80.0, 75.0, scale)
+        degenerate = (r0.abs().amax(0) == 0) & mask[0]
+    keep = ~degenerate[None]
+    assert int(degenerate.sum()) <= 4
+    gmax = float(d2.grad[keep].abs().max())
+    torch.testing.assert_close(depth.grad[keep], d2.grad[keep], rtol=1e-3, atol=1e-4 * gmax)
+    assert bool(torch.isfinite(depth.grad).all()) and float(depth.grad[~keep].abs().max() if int(degenerate.sum()) else 0.0) <= gmax
     # affine exposure
     img = torch.rand(3, H, W, generator=g).cuda().requires_grad_(True)
     M = (torch.eye(3) + 0.1 * torch.randn(3, 3, generator=g)).cuda().requires_grad_(True)

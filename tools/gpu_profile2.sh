@@ -19,7 +19,7 @@ cap() {  # name, kernel regex, skip, count, command...
   ncu -i $out/$name.ncu-rep --page raw --csv > $out/${name}_raw.csv 2>/dev/null
 }
 # C2 step: skip the warm-up steps' launches, capture one full step of library kernels
-cap c2 "^(r3_|band_|depth_sort)" 33 11 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --legs none
+cap c2 "^(r3_|band_|bucket_)" 42 14 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --legs none
 cap c3 "^(rs_render|rs_pre|ssim_)" 10 5 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --legs surfel
 cap c4 "^(spawn_|mlp_|np_|depth2normal|exposure|photo_)" 60 24 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --legs mapping
 cap sdf "^(sdf_query)" 12 2 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --legs sdf
