@@ -156,7 +156,10 @@ def algorithmic_bytes(P: int, R: int, W: int, H: int, Q: int = -1, surfel: bool 
     nch = min(4096, max(256, ((1 << 20) // max(nL, 1)) & ~7))   # band_row_chunks
     out = {
         "preprocess_fwd": (160 if surfel else 104) * P,      # 44 B in + 60 B out per Gaussian (surfel: + normal, zx, zy)
-        "depth_sort": (4 * (4 + 8 + 8) + 4 + 16 + 12) * P,   # 4 LSD passes over (u32 key, u32 value) + rect gather + weight scan
+        # bucket sort (band path): histogram reads the keys (4), scatter reads them again and writes (key, id) pairs
+        # (4 + 8), the local sort reads the pairs, gathers the rects and writes ids + rects (8 + 8 + 12); per Gaussian,
+        # counting every Gaussian as visible.  (The 4-pass LSD path moves 112 B per Gaussian.)
+        "depth_sort": (44 if os.environ.get("PG_SORT_IMPL", "b")[0] != "r" else 112) * P,
         # blend kernels: HBM sees the id list once, each record once (re-reads by other tiles hit L2) and the
         # images; the per-instance record / gradient traffic (l2_bytes below) is L2 and shared-memory work
         "render_fwd": 4 * R + (68 if surfel else 48) * P + (44 if surfel else 28) * WH,
@@ -211,8 +214,8 @@ def roofline_tables(phase_ms: dict, ab: dict, pk: dict, l2: dict | None = None):
 # launch on the C2 scene from the committed ncu --set full capture (profiles/r02_ncu_full_c2.csv,
 # smsp__inst_executed.sum; a property of the scene, not of the clock) over the kernel's LIVE duration, against the
 # B200 issue peak of 148 SMs x 4 schedulers x 1 warp-instruction / clock at the SM clock sampled during the run.
-ISSUE_INST: dict = {"render_fwd": 76315285, "render_bwd": 92457944, "preprocess_fwd": 8637648,
-                    "preprocess_bwd": 14840160, "depth_sort": 6114119}
+ISSUE_INST: dict = {"render_fwd": 76318981, "render_bwd": 92405504, "preprocess_fwd": 8841762,
+                    "preprocess_bwd": 14840160, "depth_sort": 4850044}   # depth_sort = the four bucket-sort kernels
 
 
 def issue_roofline(phase_ms: dict, sm_mhz: float, pairs: int) -> dict:
@@ -565,10 +568,10 @@ def run_ours(args, rank, world, local):
 # per-launch dram bytes (dram__bytes_read.sum + dram__bytes_write.sum) from the committed ncu --set full capture of
 # the C2 step (profiles/r02_ncu_full_c2.csv) and of the C1 SDF query (profiles/r02_ncu_full_sdf.csv); the capture
 # runs the step without the L2 flush, so inputs produced by the previous kernel are L2 hits
-TRAFFIC: dict = {"preprocess_fwd": 28.7e6, "depth_sort": 6.11e6, "band_rows_kernel<count>": 3.42e6,
+TRAFFIC: dict = {"preprocess_fwd": 28.8e6, "depth_sort": 12.7e6, "band_rows_kernel<count>": 3.42e6,
                  "band_list_scan_kernel": 1.19e6, "band_rows_kernel<write>": 6.31e6, "band_expand_kernel<count>": 15.1e6,
-                 "band_tile_scan_kernel": 2.80e6, "band_expand_kernel<write>": 51.4e6, "render_fwd": 3.53e6,
-                 "render_bwd": 13.05e6, "preprocess_bwd": 50.5e6, "sdf_query": 11.9e6}
+                 "band_tile_scan_kernel": 2.80e6, "band_expand_kernel<write>": 51.2e6, "render_fwd": 3.39e6,
+                 "render_bwd": 13.05e6, "preprocess_bwd": 50.7e6, "sdf_query": 11.7e6}
 
 
 def cpu_baseline_line(args) -> dict | None:
@@ -1107,9 +1110,8 @@ def large_map_leg(args, local, world, rank) -> dict:
                     phases.setdefault(name, []).append(pms)
         L.timing_enable(False)
         phase_ms = {k: sum(v) / len(v) for k, v in phases.items()}
-        Q = int(L.lib().pg_raster_band_records(W, H, int(R), out[8].data_ptr(), None))
+        Q = int(L.lib().pg_raster_band_records(W, H, int(RC.last_binning_capacity()), out[8].data_ptr(), None))
         ab = algorithmic_bytes(P, int(R), W, H, Q, surfel=True)
-        ab["depth_sort"] = (4 * (4 + 8 + 8 + 2 * 4) + 4 + 16 + 12) * P    # multi-kernel path: + histogram pass per digit
         per_kernel, per_phase, dom = roofline_tables(phase_ms, ab, peaks())
         res["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": per_kernel[dom]["gbs"], "peak": peaks()["hbm_gbs"],
                            "unit": "GB/s", "frac": per_kernel[dom]["frac"], "kernels": per_kernel, "phases": per_phase,

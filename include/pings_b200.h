@@ -356,7 +356,7 @@ int pg_spawn_epilogue_backward(const PgSpawnArgs* args, const PgSpawnGrads* grad
  * sum to all replicas, end barrier.  multicast_ptr: this rank's multicast address of element 0 (16-byte aligned);
  * signal_pad_ptrs_dev: device array [world] of pointers to the ranks' zero-initialised signal pads of
  * signal_pad_bytes each (torch.distributed._symmetric_memory provides all three); numel % 4 == 0.  Every rank must
- * call with the same numel / world / max_ctas (0 = 8), each on its own stream; calls on one buffer must not overlap.
+ * call with the same numel / world / max_ctas (0 = 16 at world <= 2, else 8), each on its own stream; calls on one buffer must not overlap.
  * ---------------------------------------------------------------------------------------- */
 int pg_multimem_allreduce_f32(void* multicast_ptr, const void* signal_pad_ptrs_dev, size_t signal_pad_bytes, int64_t numel,
                               int rank, int world, float scale, int max_ctas, void* stream);

@@ -91,9 +91,11 @@ int pg_multimem_allreduce_f32(void* multicast_ptr, const void* signal_pad_ptrs_d
   if (world > 32) return PG_ERR_UNSUPPORTED;
   const size_t slots = signal_pad_bytes / (sizeof(uint32_t) * (size_t)world);
   if (slots < 1) return PG_ERR_WORKSPACE;
-  // 8 CTAs already saturate the transfer (28 MB: 0.084 ms at N = 8 standalone) and leave the SMs to the kernels the
-  // exchange overlaps: inside the C2 step at N = 8, 32 CTAs cost 0.656 ms per step, 8 CTAs 0.604, 4 CTAs 0.593
-  int ctas = max_ctas > 0 ? max_ctas : 8;
+  // A few CTAs saturate the transfer (28 MB at N = 8: 0.084 ms standalone with 8 CTAs) and leave the SMs to the kernels
+  // the exchange overlaps.  C2 step, ms: N = 8: 32 CTAs 0.656, 8 CTAs 0.604 (0.590 on a high-priority stream), 4 CTAs
+  // 0.593; N = 4: 16 CTAs 0.589, 12 CTAs 0.570, 8 CTAs 0.568; N = 2 (14 MB slices): 8 CTAs 0.586, 16 CTAs 0.569,
+  // 32 CTAs 0.597 (ncclAllReduce 0.565).
+  int ctas = max_ctas > 0 ? max_ctas : (world <= 2 ? 16 : 8);
   if ((size_t)ctas > slots) ctas = (int)slots;
   const size_t n4 = (size_t)numel / 4;
   const size_t lo = n4 * (size_t)rank / (size_t)world, hi = n4 * (size_t)(rank + 1) / (size_t)world;
