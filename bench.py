@@ -762,7 +762,13 @@ def sdf_leg(args, local, world=1, rank=0, keep=None) -> dict:
                                               "ms_per_step": round(train_ms, 4)},
                     "roofline": {"bound": "hbm", "kernel": "sdf_query", "achieved": round(gbs, 1), "peak": pk["hbm_gbs"],
                                  "unit": "GB/s", "frac": round(gbs / pk["hbm_gbs"], 4), "alg_bytes_per_query": 944,
-                                 "traffic": TRAFFIC.get("sdf_query")}}}
+                                 "traffic": TRAFFIC.get("sdf_query"),
+                                 # the map is L2-resident at C1 and the kernel is issue-bound: warp instructions per query
+                                 # from profiles/r02_ncu_full_sdf.csv (half-warp kernel) over the live duration
+                                 "issue": ({"warp_inst_per_query": 666, "ginst_s": round(666 * N / (ms * 1e-3) / 1e9, 1),
+                                            "peak_ginst_s": round(ISSUE_PEAK_GINST, 1),
+                                            "frac": round(666 * N / (ms * 1e-3) / 1e9 / ISSUE_PEAK_GINST, 4)}
+                                           if os.environ.get("PG_SDF_IMPL") is None else None)}}}
 
 
 # ----------------------------------------------------------------------------------------------
