@@ -214,6 +214,7 @@ def roofline_tables(phase_ms: dict, ab: dict, pk: dict, l2: dict | None = None):
 # launch on the C2 scene from the committed ncu --set full capture (profiles/r02_ncu_full_c2.csv,
 # smsp__inst_executed.sum; a property of the scene, not of the clock) over the kernel's LIVE duration, against the
 # B200 issue peak of 148 SMs x 4 schedulers x 1 warp-instruction / clock at the SM clock sampled during the run.
+ISSUE_PEAK_GINST = 148 * 4 * 1.965      # G warp-instructions/s: 148 SMs x 4 schedulers at the 1.965 GHz maximum SM clock
 ISSUE_INST: dict = {"render_fwd": 76318981, "render_bwd": 92405504, "preprocess_fwd": 8841762,
                     "preprocess_bwd": 14840160, "depth_sort": 4850044}   # depth_sort = the four bucket-sort kernels
 
