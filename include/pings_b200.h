@@ -349,6 +349,22 @@ int pg_spawn_epilogue_forward(const PgSpawnArgs* args, const PgSpawnOut* out, vo
 int pg_spawn_epilogue_backward(const PgSpawnArgs* args, const PgSpawnGrads* grads, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Tracker registration step (utils/tracker.py:353-607 registration_step, :610-759 implicit_reg /
+ * implicit_color_reg).  pg_registration_weights: per source point the validity test (nn mask, gradient-norm window,
+ * sdf_std bound), the residual sdf_pred [/ |grad|] - label and the product of the Geman-McClure distance / gradient
+ * weights, the normal-consistency weight 0.5 + |n . grad/|grad|| and an optional extra weight; invalid points get
+ * residual = weight = 0 (no compaction); sums[4] (double) = {valid count, sum w, sum |residual|, -}.
+ * pg_normal_equations: J = [p x g, g]; out28 (double) = the 21 upper-triangle entries of sum w J^T J (row-major),
+ * the 6 entries of sum w J r, and sum w r^2.  weight may be NULL (all ones).
+ * ---------------------------------------------------------------------------------------- */
+int pg_registration_weights(int64_t N, const float* sdf_pred, const float* sdf_grad, const float* sdf_labels,
+                            const float* normals, const uint8_t* mask, const float* sdf_std, const float* w_extra,
+                            float min_grad_norm, float max_grad_norm, float max_sdf_std, float gm_dist, float gm_grad,
+                            int div_grad_norm, float* residual, float* weight, uint8_t* valid, double* sums, void* stream);
+int pg_normal_equations(int64_t N, const float* points, const float* grad, const float* residual, const float* weight,
+                        double* out28, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Gradient exchange of the data-parallel step (the reference is single-GPU, SURVEY.md 0.3, so
  * there is no reference symbol): in-place all-reduce (sum, then * scale) of a flat fp32 buffer that lives in
  * SYMMETRIC memory mapped for NVSwitch multicast on every rank, as ONE kernel: cross-GPU start barrier over the

@@ -201,6 +201,11 @@ def lib() -> C.CDLL:
     L.pg_spawn_count_index.argtypes = [C.c_int64]
     L.pg_spawn_epilogue_forward.restype = C.c_int
     L.pg_spawn_epilogue_forward.argtypes = [C.POINTER(PgSpawnArgs), C.POINTER(PgSpawnOut), fp]
+    L.pg_registration_weights.restype = C.c_int
+    L.pg_registration_weights.argtypes = [C.c_int64, fp, fp, fp, fp, fp, fp, fp, C.c_float, C.c_float, C.c_float, C.c_float,
+                                          C.c_float, C.c_int, fp, fp, fp, fp, fp]
+    L.pg_normal_equations.restype = C.c_int
+    L.pg_normal_equations.argtypes = [C.c_int64, fp, fp, fp, fp, fp, fp]
     L.pg_multimem_allreduce_f32.restype = C.c_int
     L.pg_multimem_allreduce_f32.argtypes = [fp, fp, C.c_size_t, C.c_int64, C.c_int, C.c_int, C.c_float, C.c_int, fp]
     L.pg_spawn_epilogue_forward_static.restype = C.c_int
