@@ -994,6 +994,19 @@ def mapping_leg(args, local, world, rank) -> dict:
     steps, warm = max(3, min(args.steps, 10)), 3
     for _ in range(warm):
         step()
+    if os.environ.get("PG_C4_PROFILE") and rank == 0:      # dev only: host-side cost of the step by function
+        import cProfile
+        import pstats
+        pr = cProfile.Profile()
+        torch.cuda.synchronize()
+        pr.enable()
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        pr.disable()
+        st_ = pstats.Stats(pr, stream=sys.stderr)
+        st_.sort_stats("cumulative").print_stats(45)
+        st_.sort_stats("tottime").print_stats(30)
     barrier(world)
     evs = []
     loss = None

@@ -11,7 +11,7 @@ allowed_padding = ["same", "valid"]
 
 
 def _stream(dev):
-    return torch.cuda.current_stream(dev).cuda_stream
+    return L.raw_stream(dev)
 
 
 def fusedssim(C1, C2, img1, img2, train):
@@ -26,7 +26,7 @@ def fusedssim(C1, C2, img1, img2, train):
         p = [torch.empty_like(img1) for _ in range(3)]
     else:
         p = [torch.empty(0, device=img1.device) for _ in range(3)]
-    with torch.cuda.device(img1.device):
+    with L.device_guard(img1.device):
         L.check(L.lib().pg_ssim_forward(B, CH, H, W, C1, C2, img1.data_ptr(), img2.data_ptr(), ssim_map.data_ptr(),
                                         L.ptr(p[0]), L.ptr(p[1]), L.ptr(p[2]), _stream(img1.device)), "ssim forward")
     return ssim_map, p[0], p[1], p[2]
@@ -39,7 +39,7 @@ def fusedssim_backward(C1, C2, img1, img2, dL_dmap, dm_dmu1, dm_dsigma1_sq, dm_d
     dL_dmap = dL_dmap.to(torch.float32).contiguous()
     B, CH, H, W = img1.shape
     out = torch.empty_like(img1)
-    with torch.cuda.device(img1.device):
+    with L.device_guard(img1.device):
         L.check(L.lib().pg_ssim_backward(B, CH, H, W, C1, C2, img1.data_ptr(), img2.data_ptr(), dL_dmap.data_ptr(), 0.0,
                                          dm_dmu1.data_ptr(), dm_dsigma1_sq.data_ptr(), dm_dsigma12.data_ptr(),
                                          out.data_ptr(), _stream(img1.device)), "ssim backward")
@@ -83,7 +83,7 @@ class _FusedSSIMMean(torch.autograd.Function):
         p = [torch.empty_like(a) for _ in range(3)] if need else [None] * 3
         scratch = torch.empty(1, dtype=torch.float64, device=a.device)
         mean = torch.empty((), dtype=torch.float32, device=a.device)
-        with torch.cuda.device(a.device):
+        with L.device_guard(a.device):
             L.check(L.lib().pg_ssim_mean_forward(B, CH, H, W, C1, C2, a.data_ptr(), b.data_ptr(), L.ptr(p[0]), L.ptr(p[1]),
                                                  L.ptr(p[2]), scratch.data_ptr(), mean.data_ptr(), _stream(a.device)),
                     "ssim mean forward")
@@ -98,7 +98,7 @@ class _FusedSSIMMean(torch.autograd.Function):
         B, CH, H, W = a.shape
         up = g.detach().to(torch.float32).reshape(1).contiguous()
         out = torch.empty_like(a)
-        with torch.cuda.device(a.device):
+        with L.device_guard(a.device):
             L.check(L.lib().pg_ssim_mean_backward(B, CH, H, W, a.data_ptr(), b.data_ptr(), up.data_ptr(), p0.data_ptr(),
                                                   p1.data_ptr(), p2.data_ptr(), out.data_ptr(), _stream(a.device)),
                     "ssim mean backward")

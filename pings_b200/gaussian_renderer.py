@@ -29,7 +29,7 @@ from .imgops import depth2normal, exposure_affine
 # as three CUDA kernels behind the C-ABI (pings_b200/csrc/pg_spawn.cuh): one gather before the heads, one fused
 # epilogue after them (single-pass ordered compaction, device-side count), and their adjoints.
 def _stream(dev) -> int:
-    return torch.cuda.current_stream(dev).cuda_stream
+    return L.raw_stream(dev)
 
 
 class _SpawnPrepare(torch.autograd.Function):
@@ -45,7 +45,7 @@ class _SpawnPrepare(torch.autograd.Function):
         use_view = bool(view_concat and cam_origin is not None)
         geo_in = torch.empty(n, Fg, dtype=torch.float32, device=dev)
         color_in = torch.empty(n, Fc + (3 if use_view else 0), dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             L.check(lib.pg_spawn_prepare(n, L.ptr(sidx), L.ptr(position), L.ptr(orientation), L.ptr(cam_origin),
                                          gf.data_ptr(), Fg, cf.data_ptr(), Fc, 0, int(use_view), int(bool(xy_only)),
                                          geo_in.data_ptr(), color_in.data_ptr(), _stream(dev)), "spawn prepare")
@@ -64,7 +64,7 @@ class _SpawnPrepare(torch.autograd.Function):
                 continue
             d = d.contiguous()
             g = torch.zeros(shape, dtype=torch.float32, device=d.device)
-            with torch.cuda.device(d.device):
+            with L.device_guard(d.device):
                 L.check(lib.pg_spawn_prepare_backward(ctx.n, L.ptr(ctx.sidx), d.data_ptr(), d.shape[1], shape[1],
                                                       g.data_ptr(), _stream(d.device)), "spawn prepare backward")
             outs[k] = g
@@ -99,7 +99,7 @@ class _SpawnEpilogue(torch.autograd.Function):
         o.xyz, o.scale, o.rot, o.alpha, o.color = (t.data_ptr() for t in (xyz, scale, rot, alpha, color))
         o.alpha_all, o.cpos, o.free_out, o.free_mask = alpha_all.data_ptr(), cpos.data_ptr(), L.ptr(free_out), L.ptr(c["free_mask"])
         o.state = state.data_ptr()
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             L.check(lib.pg_spawn_epilogue_forward(C.byref(a), C.byref(o), _stream(dev)), "spawn epilogue")
         ci = lib.pg_spawn_count_index(NK)
         host = state[ci:ci + 2].cpu()    # the one host read of spawn_gaussians: kept count + NaN flag (GR:305-306 assert)
@@ -132,7 +132,7 @@ class _SpawnEpilogue(torch.autograd.Function):
         g.d_alpha_all, g.cpos = L.ptr(d_alpha_all), cpos.data_ptr()
         g.d_xyz_raw, g.d_rot_raw, g.d_scale_raw = g_xyz.data_ptr(), g_rot.data_ptr(), g_scale.data_ptr()
         g.d_alpha_raw, g.d_color_raw = g_alpha.data_ptr(), g_color.data_ptr()
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             L.check(lib.pg_spawn_epilogue_backward(C.byref(ctx.args), C.byref(g), _stream(dev)), "spawn epilogue backward")
         return g_xyz, g_rot, g_scale, g_alpha, g_color, None
 

@@ -10,7 +10,7 @@ from . import _lib as L
 
 
 def _stream(dev) -> int:
-    return torch.cuda.current_stream(dev).cuda_stream
+    return L.raw_stream(dev)
 
 
 class _Depth2Normal(torch.autograd.Function):
@@ -25,7 +25,7 @@ class _Depth2Normal(torch.autograd.Function):
         m = mask.detach().contiguous().view(torch.uint8)
         a = None if alpha is None else alpha.detach().to(torch.float32).contiguous()
         out = torch.empty(3, H, W, dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             L.check(lib.pg_depth2normal_forward(H, W, cx, cy, fx, fy, d.data_ptr(), m.data_ptr(), L.ptr(a), out.data_ptr(),
                                                 _stream(dev)), "depth2normal")
         ctx.save_for_backward(d, m, a if a is not None else d.new_empty(0))
@@ -40,7 +40,7 @@ class _Depth2Normal(torch.autograd.Function):
         H, W, cx, cy, fx, fy, shape, has_alpha = ctx.k
         g = g.to(torch.float32).contiguous()
         dd = torch.empty(H, W, dtype=torch.float32, device=d.device)
-        with torch.cuda.device(d.device):
+        with L.device_guard(d.device):
             L.check(lib.pg_depth2normal_backward(H, W, cx, cy, fx, fy, d.data_ptr(), m.data_ptr(),
                                                  a.data_ptr() if has_alpha else None, g.data_ptr(), dd.data_ptr(),
                                                  _stream(d.device)), "depth2normal backward")
@@ -65,7 +65,7 @@ class _ExposureAffine(torch.autograd.Function):
         m = mat.detach().to(torch.float32).contiguous()
         o = offset.detach().to(torch.float32).reshape(3).contiguous()
         out = torch.empty(3, H, W, dtype=torch.float32, device=dev)
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             L.check(lib.pg_exposure_affine_forward(H, W, img.data_ptr(), m.data_ptr(), o.data_ptr(), out.data_ptr(),
                                                    _stream(dev)), "exposure")
         ctx.save_for_backward(img, m)
@@ -81,7 +81,7 @@ class _ExposureAffine(torch.autograd.Function):
         g = g.to(torch.float32).contiguous()
         d_img = torch.empty_like(img) if ctx.needs_input_grad[0] else None
         d12 = torch.empty(12, dtype=torch.float32, device=img.device)
-        with torch.cuda.device(img.device):
+        with L.device_guard(img.device):
             L.check(lib.pg_exposure_affine_backward(H, W, img.data_ptr(), m.data_ptr(), g.data_ptr(), L.ptr(d_img),
                                                     d12.data_ptr(), _stream(img.device)), "exposure backward")
         return d_img, d12[:9].view(3, 3), d12[9:].reshape(oshape)

@@ -194,9 +194,9 @@ class NeuralPoints(nn.Module):
         cache = getattr(self, "_mirror_cache", None)
         if cache is None or cache[0] != key:
             t32 = torch.empty(int(self.buffer_size), dtype=torch.int32, device=self.buffer_pt_index.device)
-            with torch.cuda.device(t32.device):
+            with L.device_guard(t32.device):
                 L.check(L.lib().pg_np_build_slot_mirror(int(self.buffer_size), self.buffer_pt_index.data_ptr(), t32.data_ptr(),
-                                                        torch.cuda.current_stream(t32.device).cuda_stream), "slot mirror")
+                                                        L.raw_stream(t32.device)), "slot mirror")
             self._mirror_cache = cache = (key, t32)
         return cache[1].data_ptr()
 
@@ -271,9 +271,9 @@ class NeuralPoints(nn.Module):
         o.geo_vec, o.color_vec, o.weight = L.ptr(geo_vec), L.ptr(color_vec), weight.data_ptr()
         o.nn_counts, o.certainty = nn_counts.data_ptr(), certainty.data_ptr()
         o.knn_idx, o.knn_dist2 = knn_idx.data_ptr(), knn_d.data_ptr()
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             L.check(lib.pg_np_query_feature(C.byref(m), C.byref(a), N, q.data_ptr(), C.byref(o),
-                                            torch.cuda.current_stream(dev).cuda_stream), "query_feature")
+                                            L.raw_stream(dev)), "query_feature")
         return geo_vec, color_vec, weight, nn_counts, certainty, knn_idx, knn_d
 
     def _query_backward(self, q, knn_idx, knn_d, weight, nn_counts, d_geo, d_color, d_weight, gshape, cshape, flags,
@@ -300,11 +300,11 @@ class NeuralPoints(nn.Module):
         dc = torch.zeros(cshape, dtype=torch.float32, device=dev) if cshape is not None else None
         c = lambda t: None if t is None else t.contiguous()
         d_geo, d_color, d_weight = c(d_geo), c(d_color), c(d_weight)
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             L.check(lib.pg_np_query_feature_backward(
                 C.byref(a), N, qc.data_ptr(), knn_idx.data_ptr(), knn_d.data_ptr(), weight.data_ptr(),
                 nn_counts.data_ptr(), L.ptr(d_geo), L.ptr(d_color), L.ptr(d_weight), L.ptr(dg), L.ptr(dc), L.ptr(dq),
-                torch.cuda.current_stream(dev).cuda_stream), "query_feature backward")
+                L.raw_stream(dev)), "query_feature backward")
         return dq, dg, dc
 
     # ------------------------------------------------------------------ public query API
@@ -317,9 +317,9 @@ class NeuralPoints(nn.Module):
         dist2 = torch.empty(N, K, dtype=torch.float32, device=q.device)
         idx = torch.empty(N, K, dtype=torch.int64, device=q.device)
         m = self._map_struct(time_filtering)
-        with torch.cuda.device(q.device):
+        with L.device_guard(q.device):
             L.check(lib.pg_np_radius_search(C.byref(m), N, q.data_ptr(), int(bool(time_filtering)), dist2.data_ptr(),
-                                            idx.data_ptr(), torch.cuda.current_stream(q.device).cuda_stream),
+                                            idx.data_ptr(), L.raw_stream(q.device)),
                     "radius_neighborhood_search")
         return dist2, idx
 
@@ -345,11 +345,11 @@ class NeuralPoints(nn.Module):
                 if query_locally and query_ts is not None:
                     ts = query_ts.to(torch.int32).contiguous()
                 N, k = knn_idx.shape
-                with torch.cuda.device(knn_idx.device):
+                with L.device_guard(knn_idx.device):
                     L.check(L.lib().pg_np_accumulate_stability(
                         N, k, knn_idx.data_ptr(), weight.detach().data_ptr(), L.ptr(ts), cert.data_ptr(),
                         self.local_point_ts_update.data_ptr() if ts is not None else None,
-                        torch.cuda.current_stream(knn_idx.device).cuda_stream), "accumulate_stability")
+                        L.raw_stream(knn_idx.device)), "accumulate_stability")
         return (geo_vec if geo_table is not None else None, color_vec if color_table is not None else None,
                 weight.unsqueeze(-1), nn_counts, certainty)
 
@@ -379,10 +379,10 @@ class NeuralPoints(nn.Module):
         want_std = get_std and not self.config.weighted_first
         std = torch.empty(N, dtype=torch.float32, device=dev) if want_std else None
         nn_counts = torch.empty(N, dtype=torch.int64, device=dev)
-        with torch.cuda.device(dev):
+        with L.device_guard(dev):
             L.check(lib.pg_sdf_query(C.byref(m), C.byref(a), C.byref(mlp), float(decoder.sdf_scale), N, q.data_ptr(),
                                      sdf.data_ptr(), L.ptr(std), nn_counts.data_ptr(),
-                                     torch.cuda.current_stream(dev).cuda_stream), "sdf_query")
+                                     L.raw_stream(dev)), "sdf_query")
         return sdf, std, nn_counts
 
     # ------------------------------------------------------------------ map maintenance (torch ops)
