@@ -78,6 +78,92 @@ class _MlpFn(torch.autograd.Function):
         return (None, None if dX is None else dX.reshape(*ctx.lead, x2.shape[1]), *grads)
 
 
+class _MultiMlpFn(torch.autograd.Function):
+    """Several decoders on ONE shared input as one autograd node (spawn_gaussians runs its xyz / rot / scale / alpha
+    heads on the same gathered feature matrix, GR:609-676): the same kernels as _MlpFn per head, but one
+    Function.apply and one backward node instead of one per head - the C4 step is bound by exactly that host work."""
+
+    @staticmethod
+    def forward(ctx, decs, x, *params):
+        lib = L.lib()
+        if not x.is_cuda:
+            raise RuntimeError("pings_b200.Decoder: expected CUDA tensors (there is no CPU fallback)")
+        lead = x.shape[:-1]
+        x2 = x.detach()
+        if x2.dim() != 2:
+            x2 = x2.reshape(-1, x.shape[-1])
+        if x2.dtype is not torch.float32 or not x2.is_contiguous():
+            x2 = x2.to(torch.float32).contiguous()
+        N, dev = x2.shape[0], x2.device
+        need = any(ctx.needs_input_grad[1:])
+        ys, hss = [], []
+        with L.device_guard(dev):
+            st = L.raw_stream(dev)
+            for dec in decs:
+                mlp, keep = dec._mlp_struct()
+                y = torch.empty(N, dec.mlp_out_dim, dtype=torch.float32, device=dev)
+                hs = torch.empty(dec.hidden_level, N, dec.hidden_dim, dtype=torch.float32, device=dev) if need else None
+                L.check(lib.pg_mlp_forward(C.byref(mlp), N, x2.data_ptr(), y.data_ptr(), L.ptr(hs), st), "mlp forward")
+                ys.append(y.reshape(*lead, dec.mlp_out_dim))
+                hss.append(hs)
+        if need:
+            ctx.decs, ctx.lead = decs, lead
+            ctx.save_for_backward(x2, *hss, *params)
+        return tuple(ys)
+
+    @staticmethod
+    @torch.autograd.function.once_differentiable
+    def backward(ctx, *dys):
+        lib = L.lib()
+        decs = ctx.decs
+        x2, *rest = ctx.saved_tensors
+        hss, saved = rest[:len(decs)], rest[len(decs):]
+        N, dev = x2.shape[0], x2.device
+        want_dx = ctx.needs_input_grad[1]
+        dX_total = None
+        grads = []
+        k = 0
+        with L.device_guard(dev):
+            st = L.raw_stream(dev)
+            for dec, hs, dy in zip(decs, hss, dys):
+                np_ = len(dec._params())
+                mine = saved[k:k + np_]
+                k += np_
+                if dy is None:
+                    grads += [None] * np_
+                    continue
+                dy2 = dy.reshape(N, dec.mlp_out_dim)
+                if dy2.dtype is not torch.float32 or not dy2.is_contiguous():
+                    dy2 = dy2.to(torch.float32).contiguous()
+                mlp, keep = dec._mlp_struct(mine)
+                shapes = dec._grad_layout()
+                flat = torch.zeros(shapes[-1][2], dtype=torch.float32, device=dev)
+                base = flat.data_ptr()
+                nl = len(dec.layers) + 1
+                pw, pb = (L.fp * nl)(), (L.fp * nl)()
+                j = 0
+                for i in range(nl):
+                    pw[i] = base + 4 * shapes[j][1]
+                    j += 1
+                    if dec._has_bias:
+                        pb[i] = base + 4 * shapes[j][1]
+                        j += 1
+                dX = torch.empty_like(x2) if want_dx else None
+                L.check(lib.pg_mlp_backward(C.byref(mlp), N, x2.data_ptr(), hs.data_ptr(), dy2.data_ptr(), L.ptr(dX), pw, pb,
+                                            st), "mlp backward")
+                grads += [flat[o:e].view(shp) for shp, o, e in shapes[:-1]]
+                if dX is not None:
+                    dX_total = dX if dX_total is None else dX_total.add_(dX)
+        return (None, None if dX_total is None else dX_total.reshape(*ctx.lead, x2.shape[1]), *grads)
+
+
+def mlp_multi(decs, x):
+    """[dec.mlp(x) for dec in decs] as one autograd node (all decoders take the same input)."""
+    decs = tuple(decs)
+    params = [p for d in decs for p in d._params()]
+    return list(_MultiMlpFn.apply(decs, x, *params))
+
+
 MLP_AUTO, MLP_SIMT, MLP_TCGEN05 = 0, 1, 2
 
 

@@ -20,6 +20,7 @@ from typing import Dict, Optional
 import torch
 
 from . import _lib as L
+from .decoder import mlp_multi
 from .imgops import depth2normal, exposure_affine
 
 
@@ -179,17 +180,20 @@ def spawn_gaussians(neural_points_data: Dict, decoders: Dict, visible_mask: Opti
     cam_c = f32c(cam_origin)
     geo_in, color_in = _SpawnPrepare.apply(geo_features, color_features, sidx, n_pts, pos_c, quat_c, cam_c,
                                            bool(view_concat_on), bool(view_direction_xy_only))
-    xyz_raw = xyz_mlp.mlp_batch(geo_in)
-    rot_raw = rot_mlp.mlp_batch(geo_in)
-    scale_raw = scale_mlp.mlp_batch(geo_in)
-    alpha_in = geo_in
-    if dist_concat_on and cam_c is not None:   # GR:677-678: the view distance feeds the alpha head only
+    # the heads that read the gathered geo features run as ONE autograd node (decoder.mlp_multi: same kernels, a
+    # quarter of the Function / backward-node overhead); GR:609-676 calls them one by one
+    shared_alpha = not (dist_concat_on and cam_c is not None)
+    heads = [xyz_mlp, rot_mlp, scale_mlp] + ([alpha_mlp] if shared_alpha else [])
+    outs = mlp_multi(heads, geo_in)
+    xyz_raw, rot_raw, scale_raw = outs[0], outs[1], outs[2]
+    if shared_alpha:
+        alpha_raw = outs[3]
+    else:                                        # GR:677-678: the view distance feeds the alpha head only
         p_sel = pos_c if sidx is None else pos_c.index_select(0, sidx)
         vd = p_sel - cam_c
         if view_direction_xy_only:
             vd = torch.cat((vd[:, :2], torch.zeros_like(vd[:, 2:])), 1)
-        alpha_in = torch.cat((geo_in, vd.norm(dim=1, keepdim=True)), dim=1)
-    alpha_raw = alpha_mlp.mlp_batch(alpha_in)
+        alpha_raw = alpha_mlp.mlp_batch(torch.cat((geo_in, vd.norm(dim=1, keepdim=True)), dim=1))
     color_raw = color_mlp.mlp_batch(color_in)
 
     shifted_position = None
