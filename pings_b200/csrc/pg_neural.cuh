@@ -146,81 +146,124 @@ __device__ __forceinline__ void np_lane_deltas(const NpMapDev& m, int lane, long
   }
 }
 
+// Since round 2 (same scheme as sdf_query_half_kernel, pg_sdf.cuh): the slot-table loads of a lane are issued back to
+// back, the OCCUPIED slots (about 8 of 81) are compacted by ballot + popc into per-warp shared memory in probe order,
+// distances / masks / local indices are computed only for those, and the nn_k nearest are picked by rank counting over
+// the surviving candidates - rank = number of candidates with a smaller (distance bits, probe position) key, i.e. the
+// stable order of torch.sort over the probe axis (NP:565); keys are unique.  Before: every lane did the distance
+// arithmetic of its CPL probes and the selection took nn_k arg-min rounds of 2 REDUX + bookkeeping (a third of the
+// instructions of a query).  Callers run with 8 warps per CTA (kNpWarps / kSdfWarps).
+constexpr int kNpKnnWarps = 8;
+
 template <int CPL>
 __device__ __forceinline__ int np_warp_knn(const NpMapDev& m, const NpQueryDev& a, const long long (&dh)[CPL],
                                            const uint32_t (&dr)[CPL], float qx, float qy, float qz, int lane, float& sel_d,
                                            int& sel_i) {
+  constexpr int kSlots = CPL * 32;
+  __shared__ uint32_t s_hit[kNpKnnWarps][2][kSlots];          // occupied slots: point index, probe position
+  __shared__ unsigned long long s_key[kNpKnnWarps][kSlots];  // candidates: dist bits << 32 | probe position
+  __shared__ uint32_t s_val[kNpKnnWarps][kSlots];            // candidates: final (local) index
+  __shared__ float s_od[kNpKnnWarps][kNpMaxK];
+  __shared__ int s_oi[kNpKnnWarps][kNpMaxK];
+  const int wp = (threadIdx.x >> 5) & (kNpKnnWarps - 1);
+  uint32_t* hit_i = s_hit[wp][0];
+  uint32_t* hit_p = s_hit[wp][1];
+  unsigned long long* ck = s_key[wp];
+  uint32_t* cv = s_val[wp];
   const long long h0 = np_hash_base(m, np_cell(qx, m.res), np_cell(qy, m.res), np_cell(qz, m.res));
   // fast path: no int64 wrap possible in h0 + dh (|h0| < 2^62, |dh| < 2^40) and 32-bit slots
   const bool fast = m.buffer_size < (1ll << 31) && h0 > -(1ll << 62) && h0 < (1ll << 62);
   const uint32_t b0 = fast ? (uint32_t)np_slot_of(m, h0) : 0u;
   const uint32_t d32 = (uint32_t)m.buffer_size;
-  float cd[CPL];
-  int ci[CPL];
-  int cnt = 0;
+  // ---- phase 1: slot-table probes ----
+  long long pidx[CPL];
 #pragma unroll
   for (int c = 0; c < CPL; ++c) {
-    const int k = c * 32 + lane;
-    cd[c] = kNpInvalidDist;
-    ci[c] = -1;
-    if (k < m.K) {
-      long long idx;
-      float d;
+    pidx[c] = -1;
+    if (c * 32 + lane < m.K) {
+      long long slot;
       if (fast) {
-        uint32_t slot = b0 + dr[c];
-        if (slot >= d32) slot -= d32;
-        np_probe_slot(m, (long long)slot, qx, qy, qz, idx, d);
+        uint32_t sl = b0 + dr[c];
+        if (sl >= d32) sl -= d32;
+        slot = (long long)sl;
       } else {
-        np_probe_h(m, (long long)((unsigned long long)h0 + (unsigned long long)dh[c]), qx, qy, qz, idx, d);
+        slot = np_slot_of(m, (long long)((unsigned long long)h0 + (unsigned long long)dh[c]));
       }
-      if (idx >= 0) {
-        if (a.use_only_measured && a.free_mask[idx]) idx = -1;
-        if (idx >= 0 && a.use_only_valid && !a.valid_mask[idx]) idx = -1;
-        if (idx >= 0 && a.query_locally) idx = a.g2l[idx];
-      }
-      if (idx >= 0) {
-        cd[c] = d;
-        ci[c] = (int)idx;
-        ++cnt;
-      }
+      pidx[c] = m.table32 ? (long long)m.table32[slot] : m.table[slot];
     }
   }
-  cnt = __reduce_add_sync(0xffffffffu, cnt);
-  sel_d = kNpInvalidDist;
-  sel_i = -1;
-  const int rounds = min(a.nn_k, cnt);  // the remaining slots are invalid (dist 9e3, idx -1)
-  for (int j = 0; j < rounds; ++j) {
-    // local best (lowest distance, ties -> lowest probe position, i.e. a stable sort)
-    float bd = kNpInvalidDist * 2.f;
-    int bk = 0x7fffffff;
+  if (m.time_filtering) {
 #pragma unroll
     for (int c = 0; c < CPL; ++c) {
-      if (ci[c] >= 0 && cd[c] < bd) {
-        bd = cd[c];
-        bk = c * 32 + lane;
+      if (pidx[c] >= 0) {
+        const float diff = fabsf(m.travel[m.cur_ts] - m.travel[m.ts_create[pidx[c]]]);
+        if (!(diff < m.diff_local)) pidx[c] = -1;
       }
     }
-    // warp arg-min with two REDUX: distances are >= +0, so their bit patterns order like the values;
-    // among the lanes holding the minimum the lowest probe position wins
-    const uint32_t mn = __reduce_min_sync(0xffffffffu, __float_as_uint(bd));
-    bk = (int)__reduce_min_sync(0xffffffffu, __float_as_uint(bd) == mn ? (uint32_t)bk : 0xffffffffu);
-    bd = __uint_as_float(mn);
-    const int owner = bk & 31, slot = bk >> 5;
-    int oi = -1;
+  }
+  // ---- phase 2: compact the occupied slots, in probe order ----
+  const uint32_t below = (1u << lane) - 1u;
+  uint32_t nhit = 0;
 #pragma unroll
-    for (int c = 0; c < CPL; ++c)
-      if (c == slot) oi = ci[c];
-    oi = __shfl_sync(0xffffffffu, oi, owner);
-    if (lane == owner) {
-#pragma unroll
-      for (int c = 0; c < CPL; ++c)
-        if (c == slot) ci[c] = -1;
+  for (int c = 0; c < CPL; ++c) {
+    const bool hit = pidx[c] >= 0;
+    const uint32_t bm = __ballot_sync(0xffffffffu, hit);
+    if (hit) {
+      const uint32_t r = nhit + __popc(bm & below);
+      hit_i[r] = (uint32_t)pidx[c];
+      hit_p[r] = (uint32_t)(c * 32 + lane);
     }
-    if (lane == j) {
-      sel_d = bd;
-      sel_i = oi;
+    nhit += __popc(bm);
+  }
+  __syncwarp();
+  // ---- phase 3: distances (np_probe_slot's arithmetic), masks, local index; compact the survivors ----
+  uint32_t ncand = 0;
+  for (uint32_t t0 = 0; t0 < nhit; t0 += 32) {
+    const uint32_t t = t0 + lane;
+    long long idx = -1;
+    float d = 0.f;
+    uint32_t pos = 0;
+    if (t < nhit) {
+      idx = (long long)hit_i[t];
+      pos = hit_p[t];
+      const float sx = __fsub_rn(m.pts[3 * idx + 0], qx);
+      const float sy = __fsub_rn(m.pts[3 * idx + 1], qy);
+      const float sz = __fsub_rn(m.pts[3 * idx + 2], qz);
+      d = __fadd_rn(__fadd_rn(__fmul_rn(sx, sx), __fmul_rn(sy, sy)), __fmul_rn(sz, sz));
+      if (d > m.max_valid) idx = -1;
+      if (idx >= 0 && a.use_only_measured && a.free_mask[idx]) idx = -1;
+      if (idx >= 0 && a.use_only_valid && !a.valid_mask[idx]) idx = -1;
+      if (idx >= 0 && a.query_locally) idx = a.g2l[idx];
+    }
+    const bool ok = idx >= 0;
+    const uint32_t bm = __ballot_sync(0xffffffffu, ok);
+    if (ok) {
+      const uint32_t r = ncand + __popc(bm & below);
+      ck[r] = ((unsigned long long)__float_as_uint(d) << 32) | (unsigned long long)pos;
+      cv[r] = (uint32_t)idx;
+    }
+    ncand += __popc(bm);
+  }
+  __syncwarp();
+  const int cnt = (int)ncand;
+  // ---- phase 4: nn_k nearest by rank counting ----
+  for (uint32_t t = lane; t < ncand; t += 32) {
+    const unsigned long long key = ck[t];
+    uint32_t rank = 0;
+    for (uint32_t k = 0; k < ncand; ++k) rank += ck[k] < key ? 1u : 0u;
+    if (rank < (uint32_t)a.nn_k) {
+      s_od[wp][rank] = __uint_as_float((uint32_t)(key >> 32));
+      s_oi[wp][rank] = (int)cv[t];
     }
   }
+  __syncwarp();
+  sel_d = kNpInvalidDist;
+  sel_i = -1;
+  if (lane < min(a.nn_k, cnt)) {
+    sel_d = s_od[wp][lane];
+    sel_i = s_oi[wp][lane];
+  }
+  __syncwarp();   // the warp's next query overwrites the scratch
   return cnt;
 }
 
