@@ -211,7 +211,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     dL_dmeans2D = torch.empty(P, 3, **fopt)
     dL_dcov3D = torch.empty(P, 6, **fopt)
     dL_dsh = torch.empty(P, M, 3, **fopt)
-    dL_dtau = torch.zeros(1, 6, **fopt)
+    # written in full by the last block of the per-Gaussian backward; the library is not called when P == 0
+    dL_dtau = torch.empty(1, 6, **fopt) if P != 0 else torch.zeros(1, 6, **fopt)
     tau_full = torch.empty(P, 6, **fopt) if full_tau else None
     if P != 0:
         background, means3D, colors = _f32c(background), _f32c(means3D), _f32c(colors)
@@ -313,7 +314,8 @@ def rasterize_gaussians_surfel_backward(background, means3D, radii, colors, scal
     dL_dmeans2D = torch.empty(P, 3, **fopt)
     dL_dcov3D = torch.empty(P, 6, **fopt)
     dL_dsh = torch.empty(P, M, 3, **fopt)
-    dL_dtau = torch.zeros(1, 6, **fopt)
+    # written in full by the last block of the per-Gaussian backward; the library is not called when P == 0
+    dL_dtau = torch.empty(1, 6, **fopt) if P != 0 else torch.zeros(1, 6, **fopt)
     tau_full = torch.empty(P, 6, **fopt) if full_tau else None
     if P != 0:
         V = L.PG_VARIANT_SURFEL

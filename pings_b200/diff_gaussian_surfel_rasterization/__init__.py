@@ -79,7 +79,8 @@ class _RasterizeGaussians(torch.autograd.Function):
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp, grad_sh, grad_scales,
          grad_rotations, grad_tau) = res
         # the kernel already reduced dL_dtau over surfels ([1,6]); same slicing as the reference
-        grad_tau = torch.sum(grad_tau.view(-1, 6), dim=0)
+        # the kernel already reduced the pose gradient over the Gaussians to [1,6] (the reference sums [P,6] here)
+        grad_tau = grad_tau.view(6) if grad_tau.numel() == 6 else torch.sum(grad_tau.view(-1, 6), dim=0)
         grad_theta = grad_tau[3:].view(1, -1)
         grad_rho = grad_tau[:3].view(1, -1)
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities, grad_scales,
