@@ -91,6 +91,13 @@ def _worker(rank: int, ws: int, port: int, q):
                 dist.all_gather(gl, t)
                 ok &= torch.allclose(p.grad, torch.stack(gl).mean(0), rtol=0, atol=1e-6)
                 ok &= p.grad.data_ptr() >= red2.flat.data_ptr()
+        # multimem=True off CUDA: the exchange stays the collective (the NVSwitch kernel needs symmetric CUDA memory)
+        a3 = torch.nn.Parameter(torch.ones(4) * (rank + 1))
+        red3 = PP.FlatGradAllReduce([a3], average=False, multimem=True)
+        ok &= red3.backend == "collective"
+        a3.grad = torch.ones(4) * (rank + 1)
+        red3()
+        ok &= torch.equal(a3.grad, torch.full((4,), 3.0))
         # query-row sharding: the union of the shards reproduces the full result
         full = torch.arange(10, dtype=torch.float32) ** 2
         lo, hi = PP.shard_rows(10, rank, ws)
