@@ -14,7 +14,7 @@
 //   local sort   one warp (= one 32-thread CTA) per bucket: bitonic network held in registers (all comparators
 //                ascending, padding with the +inf pair), writes sorted_idx and gathers the rects; buckets above 512
 //                pairs (a bin holding hundreds of Gaussians within 2^shift depth-bit values of each other) are
-//                sorted by the same warp in place in global memory.
+//                sorted by the same warp with an LSD radix sort in global memory over the bits that differ.
 // No grid-wide barriers, no MATCH.ANY ranking chains; the culled Gaussians (key 0xFFFFFFFF) never enter.
 #pragma once
 #include "pg_common.cuh"
@@ -271,38 +271,75 @@ __device__ __forceinline__ void bucket_warp_sort(const BucketSortArgs& a, uint32
   }
 }
 
-// CTA-wide bitonic sort of d[0..n) (shared or global memory), same all-ascending network with virtual padding.
-__device__ __forceinline__ void cta_bitonic(unsigned long long* d, uint32_t n) {
-  uint32_t m = 2;
-  while (m < n) m <<= 1;
-  for (uint32_t k = 2; k <= m; k <<= 1) {
-    const uint32_t h = k >> 1;
-    for (uint32_t t = threadIdx.x; t < (m >> 1); t += blockDim.x) {
-      const uint32_t blk = t / h, off = t - blk * h;
-      const uint32_t i = blk * k + off, p = blk * k + (k - 1 - off);
-      if (p < n) {
-        const unsigned long long x = d[i], y = d[p];
-        if (y < x) { d[i] = y; d[p] = x; }
-      }
+// Fallback for a bucket above 512 pairs: a bin that holds many Gaussians within 2^shift depth-bit values of each other
+// (a facade seen head-on: tens of thousands of Gaussians inside a millimetre of depth).  One warp sorts the bucket with
+// a stable LSD radix sort over the bits that actually differ - composite = (key - bucket min) << idx_bits | idx - in
+// global memory, ping-ponging between the pair array and the bucket's own slice of `srect` (same 8 bytes per item,
+// written for real afterwards).  O(n) per 8-bit digit with ballot ranking; a bitonic network in global memory (the
+// first version of this path) needed ~100 ms for 50,000 pairs, this ~1 ms.
+__device__ __forceinline__ unsigned long long* warp_lsd_sort_pairs(unsigned long long* src, unsigned long long* dst, uint32_t n,
+                                                                   int lane, uint32_t kmin, int key_bits, int idx_bits,
+                                                                   uint32_t* cnt /* shared [256] */) {
+  const uint32_t below = (1u << lane) - 1u;
+  const unsigned long long idx_mask = (1ull << idx_bits) - 1ull;
+  for (int sh = 0; sh < key_bits + idx_bits; sh += 8) {
+    for (int k = lane; k < 256; k += 32) cnt[k] = 0u;
+    __syncwarp();
+    for (uint32_t i = lane; i < n; i += 32) {
+      const unsigned long long p = src[i];
+      const unsigned long long c = ((unsigned long long)((uint32_t)(p >> 32) - kmin) << idx_bits) | (p & idx_mask);
+      atomicAdd(&cnt[(uint32_t)(c >> sh) & 255u], 1u);
     }
-    __syncthreads();
-    for (uint32_t j = k >> 2; j >= 1; j >>= 1) {
-      for (uint32_t t = threadIdx.x; t < (m >> 1); t += blockDim.x) {
-        const uint32_t i = ((t & ~(j - 1)) << 1) | (t & (j - 1)), p = i + j;
-        if (p < n) {
-          const unsigned long long x = d[i], y = d[p];
-          if (y < x) { d[i] = y; d[p] = x; }
-        }
+    __syncwarp();
+    {   // exclusive scan of the 256 counters: lane owns 8 consecutive ones
+      uint32_t v[8], t = 0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { v[k] = cnt[lane * 8 + k]; t += v[k]; }
+      uint32_t inc = t;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
       }
-      __syncthreads();
+      uint32_t run = inc - t;
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { cnt[lane * 8 + k] = run; run += v[k]; }
     }
+    __syncwarp();
+    for (uint32_t base = 0; base < n; base += 32) {
+      const uint32_t i = base + lane;
+      const bool valid = i < n;
+      unsigned long long p = 0ull;
+      uint32_t d = 0u;
+      if (valid) {
+        p = src[i];
+        const unsigned long long c = ((unsigned long long)((uint32_t)(p >> 32) - kmin) << idx_bits) | (p & idx_mask);
+        d = (uint32_t)(c >> sh) & 255u;
+      }
+      uint32_t m = __ballot_sync(0xffffffffu, valid);      // lanes holding the same digit
+#pragma unroll
+      for (int bit = 0; bit < 8; ++bit) {
+        const uint32_t bb = __ballot_sync(0xffffffffu, (d >> bit) & 1u);
+        m &= ((d >> bit) & 1u) ? bb : ~bb;
+      }
+      uint32_t pos = 0u;
+      if (valid) pos = cnt[d] + __popc(m & below);
+      __syncwarp();
+      if (valid && (m & below) == 0u) cnt[d] += __popc(m);
+      __syncwarp();
+      if (valid) dst[pos] = p;
+    }
+    __syncwarp();
+    unsigned long long* t = src; src = dst; dst = t;
   }
+  return src;   // where the sorted bucket lives
 }
 
 // One bucket per 32-thread CTA: the bucket size is then uniform for the compiler as well (no WARPSYNC around the
-// shuffles).  Buckets above 512 pairs - a bin holding hundreds of Gaussians within 2^shift depth-bit values of each
-// other - are sorted in place in global memory by the same warp: correct for any input, slow only for those.
+// shuffles).  Buckets of up to 512 pairs are sorted in registers, larger ones by the LSD fallback above.
 __global__ void __launch_bounds__(32) bucket_local_sort_kernel(const BucketSortArgs a) {
+  __shared__ uint32_t cnt[256];
   const int lane = threadIdx.x;
   const uint32_t b = blockIdx.x;
   pdl_wait();
@@ -315,7 +352,22 @@ __global__ void __launch_bounds__(32) bucket_local_sort_kernel(const BucketSortA
     bucket_warp_sort<16>(a, s, n, lane);
   } else {
     unsigned long long* d = a.pairs + s;
-    cta_bitonic(d, n);
+    uint32_t kmin = 0xffffffffu, kmax = 0u;
+    for (uint32_t i = lane; i < n; i += 32) {
+      const uint32_t k = (uint32_t)(d[i] >> 32);
+      kmin = min(kmin, k);
+      kmax = max(kmax, k);
+    }
+    kmin = __reduce_min_sync(0xffffffffu, kmin);
+    kmax = __reduce_max_sync(0xffffffffu, kmax);
+    const int key_bits = 32 - __clz(kmax - kmin);
+    const int idx_bits = max(1, 32 - __clz(a.n - 1u));
+    unsigned long long* tmp = reinterpret_cast<unsigned long long*>(a.srect + s);
+    unsigned long long* res = warp_lsd_sort_pairs(d, tmp, n, lane, kmin, key_bits, idx_bits, cnt);
+    if (res != d) {
+      for (uint32_t i = lane; i < n; i += 32) d[i] = res[i];
+      __syncwarp();
+    }
     for (uint32_t i = lane; i < n; i += 32) {
       const uint32_t id = (uint32_t)d[i];
       a.sorted_idx[s + i] = id;

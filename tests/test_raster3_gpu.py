@@ -309,6 +309,7 @@ def test_binning_lists_bitexact_edge_cases(P, W, H, seed, scale_mul):
     (6000, 1, "bucket"),       # every visible Gaussian at (nearly) one depth: one bin, global-memory path
     (9000, 8, "bucket"),       # eight depth clusters of ~1100: shared-memory CTA path
     (40000, 300, "bucket"),    # ~130 per cluster + outlier: warp networks of every size
+    (50000, 2, "bucket"),      # two depth slabs of ~25,000 next to a far outlier (wide key range, coarse bins): the LSD fallback at scale
     (40000, 0, "bucket"),
     (40000, 0, "radix"),
 ])
@@ -333,7 +334,7 @@ def test_depth_order_bitexact_degenerate_depths(P, clusters, impl, monkeypatch):
         znew = lo + 0.5 * (hi - lo) + (q - 0.5 * (clusters - 1)) * (hi - lo) / max(clusters, 1)
         pv = torch.stack([pv[:, 0] * znew / z, pv[:, 1] * znew / z, znew, pv[:, 3]], 1)   # same pixel, new depth
         sc["means3D"] = (pv @ torch.linalg.inv(view))[:, :3].contiguous()
-        if clusters == 300:
+        if clusters in (300, 2):
             sc["means3D"][0] = sc["means3D"][0] + (sc["means3D"][0] - center) * 2000.0    # far outlier on the same ray
     bg = torch.zeros(3, device="cuda")
     R, color, radii, geom, binning, img, depth, opac, n_touched = _mine_forward(cam, sc, mats, W, H, bg, debug=True)
